@@ -1,0 +1,174 @@
+/* insb200.h -- C ABI of libinsb200.so: the B200-native (sm_100a) time-stepping core that sits
+ * behind the operator API of IncompressibleNavierStokes.jl (reference, Julia, v2.2.0).
+ *
+ * The reference has no FFI today: its operators are Julia generic functions `op!(out, in..., setup)`.
+ * Every entry point below replaces the body of one of them for the periodic, uniform-grid hot path
+ * (src/utils.jl:1-13 defines that domain); the reference function it replaces is cited as
+ * `file:line` (relative to the reference tree).  INTEGRATION.md shows the `ccall` stubs.
+ *
+ * Conventions
+ *  - every function returns 0 on success, non-zero on failure; the message is available from
+ *    insb200_last_error(ctx) (ctx == NULL: message of the last failed insb200_create).
+ *  - "device field" arguments are raw CUDA device pointers to arrays in the REFERENCE LAYOUT:
+ *    column-major, one ghost volume each side: scalar (N1,..,ND), vector (N1,..,ND,D) with
+ *    N_a = nlocal_a + 2 (src/grid.jl:121, src/initializers.jl:1-6).  The caller owns them.
+ *  - dtype: 0 = Float32, 1 = Float64.  All arithmetic is done in that type.
+ *  - calls are asynchronous on the stream given by insb200_set_stream (default: a stream owned
+ *    by the ctx), except the reductions and *_host calls, which synchronise before returning.
+ *  - one ctx per GPU / per process rank.  With nranks > 1 the domain is slab-decomposed along the
+ *    LAST axis (z in 3-D, y in 2-D): rank r owns n_last/nranks consecutive planes, device fields
+ *    are the local ghosted slabs and the ghost planes of the last axis are filled over NCCL.
+ *  - a ctx is not thread-safe; distinct ctx are independent.
+ */
+#ifndef INSB200_H
+#define INSB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct insb200_ctx insb200_ctx;
+
+#define INSB200_F32 0
+#define INSB200_F64 1
+#define INSB200_NCCL_ID_BYTES 128
+#define INSB200_MAX_STAGES 16
+
+/* ---- life cycle ---------------------------------------------------------------------------- */
+
+/* Library version (major*10000 + minor*100 + patch). */
+int insb200_version(void);
+
+/* Fill a 128-byte NCCL unique id (call on rank 0, broadcast it out of band, pass to create). */
+int insb200_comm_unique_id(void *id128);
+
+/* Replaces Setup(...)'s device side + psolver_spectral(setup) construction + ode_method_cache:
+ * src/setup.jl:2-46, src/pressure.jl:289-316, src/time_steppers/time_stepper_caches.jl:34-49.
+ *   D        2 or 3
+ *   n[D]     GLOBAL number of cells per axis (all even, utils.jl:10-12); n[D-1] % nranks == 0
+ *   dtype    INSB200_F32 / INSB200_F64
+ *   h[D]     uniform spacing per axis (Delta[a][1] of the reference grid)
+ *   Re       Reynolds number
+ *   device   CUDA device ordinal
+ *   rank, nranks, nccl_id   slab decomposition (nccl_id may be NULL when nranks == 1) */
+int insb200_create(insb200_ctx **ctx, int D, const int *n, int dtype, const double *h, double Re,
+                   int device, int rank, int nranks, const void *nccl_id);
+int insb200_destroy(insb200_ctx *ctx);
+const char *insb200_last_error(const insb200_ctx *ctx);
+int insb200_set_stream(insb200_ctx *ctx, void *cuda_stream);
+int insb200_synchronize(insb200_ctx *ctx);
+
+/* Local slab geometry: nloc[D] interior cells of this rank, offset of its first plane on the last axis. */
+int insb200_local_geometry(const insb200_ctx *ctx, int *nloc, int *last_axis_offset);
+
+/* ---- operators on device fields (reference layout) ----------------------------------------- */
+
+/* apply_bc_u!(u, t, setup), PeriodicBC: src/boundary_conditions.jl:159-167, 276-288 */
+int insb200_apply_bc_u(insb200_ctx *ctx, void *u);
+/* apply_bc_p!(p, t, setup), PeriodicBC: src/boundary_conditions.jl:197-206, 306-318 */
+int insb200_apply_bc_p(insb200_ctx *ctx, void *p);
+
+/* Steady body force field stored by Setup (src/setup.jl:25-32), consumed by applybodyforce!
+ * (src/operators.jl:861-879).  `f` = device vector field in reference layout, copied; NULL clears. */
+int insb200_set_bodyforce(insb200_ctx *ctx, const void *f);
+
+/* momentum!(F, u, temp=nothing, t, setup): src/operators.jl:967-976 (fill! + convectiondiffusion!
+ * :634-690 + applybodyforce! :861-879).  Ghosts of u must be valid; ghosts of F are set to 0. */
+int insb200_momentum(insb200_ctx *ctx, void *F, const void *u, double t);
+
+/* convection! / diffusion! / convectiondiffusion! applied to a zero field:
+ * src/operators.jl:378-415, 537-573, 634-690.  terms: 1 = convection, 2 = diffusion, 3 = both. */
+int insb200_convectiondiffusion(insb200_ctx *ctx, void *F, const void *u, int terms);
+
+/* smagorinsky_closure(setup)(u, theta): src/operators.jl:1294-1305 (smagtensor! :1135-1151,
+ * apply_bc_p!(sigma), divoftensor! :1166-1238).  Writes s; ghosts of s are set to 0. */
+int insb200_smagorinsky(insb200_ctx *ctx, void *s, const void *u, double theta);
+
+/* divergence!(div, u, setup): src/operators.jl:106-125 (interior written, ghosts untouched) */
+int insb200_divergence(insb200_ctx *ctx, void *div, const void *u);
+/* scalewithvolume!(p, setup): src/operators.jl:81-95 (whole array incl. ghosts) */
+int insb200_scalewithvolume(insb200_ctx *ctx, void *p);
+/* pressuregradient!(G, p, setup): src/operators.jl:159-178 (interior written) */
+int insb200_pressuregradient(insb200_ctx *ctx, void *G, const void *p);
+/* applypressure!(u, p, setup): src/operators.jl:214-233 */
+int insb200_applypressure(insb200_ctx *ctx, void *u, const void *p);
+
+/* psolver_spectral(setup)(p) == poisson!(psolver, p): src/pressure.jl:22, 318-350.
+ * In: volume-scaled right-hand side in p[Ip]; out: solution in p[Ip] (ghosts untouched). */
+int insb200_psolve_spectral(insb200_ctx *ctx, void *p);
+
+/* project!(u, setup; psolver, p): src/pressure.jl:69-82.  p (nullable) receives the multiplier
+ * with its ghosts filled. Ghosts of u are left as the reference leaves them (not refreshed). */
+int insb200_project(insb200_ctx *ctx, void *u, void *p);
+
+/* pressure!(p, u, temp=nothing, t, setup; psolver, F): src/pressure.jl:41-49. */
+int insb200_pressure(insb200_ctx *ctx, void *p, const void *u, double t);
+
+/* ---- reductions (synchronise; results on the host) ----------------------------------------- */
+
+/* get_cfl_timestep!(buf, u, setup): src/solver.jl:101-125 (the caller multiplies by cfl) */
+int insb200_cfl_dt(insb200_ctx *ctx, const void *u, double *dt);
+/* total_kinetic_energy(u, setup) / energy_history_plot: src/operators.jl:1516-1556,
+ * ext/IncompressibleNavierStokesMakieExt.jl:281-295 */
+int insb200_kinetic_energy(insb200_ctx *ctx, const void *u, double *E);
+/* maximum(abs, u) of timelogger: src/processors.jl:67 */
+int insb200_maxabs(insb200_ctx *ctx, const void *u, double *m);
+
+/* ---- time stepping -------------------------------------------------------------------------- */
+
+/* timestep!(::ExplicitRungeKuttaMethod, stepper, dt; theta, cache):
+ * src/time_steppers/step_explicit_runge_kutta.jl:4-59.
+ *   u      device vector field (reference layout), advanced in place, all ghosts valid on return
+ *   s,A,c  SHIFTED tableau of runge_kutta_method (src/time_steppers/methods.jl:231-236):
+ *          A is s*s row-major, c has s entries (RK44: RKMethods.jl:515-521)
+ *   theta  Smagorinsky constant; NaN = no closure model (setup.closure_model === nothing)
+ *   p_out  nullable device scalar field receiving the last stage's multiplier p (ghosts filled) */
+int insb200_rk_step(insb200_ctx *ctx, void *u, double t, double dt, int s, const double *A,
+                    const double *c, double theta, void *p_out);
+
+/* nsteps calls of timestep! with fixed dt (the fixed-step loop of solve_unsteady,
+ * src/solver.jl:71-79) without leaving the device.  *t is advanced.  ke_hist (nullable, host,
+ * nsteps+1 doubles) receives the total kinetic energy before the first and after every step. */
+int insb200_rk_steps(insb200_ctx *ctx, void *u, double *t, double dt, int nsteps, int s,
+                     const double *A, const double *c, double theta, double *ke_hist);
+
+/* solve_unsteady(; setup, tlims, ustart, method, dt, cfl, n_adapt_dt, theta) with HOST buffers:
+ * src/solver.jl:18-92.  u_host: reference-layout vector field in host memory (pinned or not),
+ * copied to the device, advanced from t0 to tend, copied back.  dt <= 0 selects the adaptive
+ * loop (:53-69) with `cfl` and `n_adapt_dt`; dt > 0 the fixed loop (:71-79, dt re-derived from
+ * round((tend-t0)/dt)).  max_steps > 0 bounds the number of steps.  ke_hist (nullable) holds
+ * ke_cap doubles: energy at start and after every step while it fits.  Outputs: number of steps
+ * taken and the final time. */
+int insb200_solve_unsteady_host(insb200_ctx *ctx, void *u_host, double t0, double tend, double dt,
+                                double cfl, int n_adapt_dt, int max_steps, int s, const double *A,
+                                const double *c, double theta, double *ke_hist, int ke_cap,
+                                int *nsteps_out, double *t_out);
+
+/* ---- introspection --------------------------------------------------------------------------- */
+
+/* Algorithmic bytes per cell per RK step of the current configuration (SURVEY.md 8d model:
+ * (46 D + 8) words + D words/stage with a stored body force). */
+double insb200_model_bytes_per_cell_step(const insb200_ctx *ctx, int nstages);
+
+/* Number of kernels of this library launched so far on this ctx, and of cuFFT executions. */
+long long insb200_launch_count(const insb200_ctx *ctx);
+long long insb200_fft_exec_count(const insb200_ctx *ctx);
+
+/* Per-kernel device timers (CUDA events on the launching stream).  enable=1 starts recording
+ * every launch; insb200_timers synchronises and returns up to `cap` entries: name (static
+ * string), accumulated milliseconds, launch count.  Returns the number of entries via *n. */
+int insb200_set_profiling(insb200_ctx *ctx, int enable);
+int insb200_timers(insb200_ctx *ctx, const char **names, double *ms, long long *counts, int cap, int *n);
+int insb200_reset_timers(insb200_ctx *ctx);
+
+/* Kernel variant switch for A/B runs: 0 = reference-structure kernels (one thread per cell,
+ * direct global loads), 1 = tiled shared-memory kernels (default where available). */
+int insb200_set_variant(insb200_ctx *ctx, int variant);
+
+/* Device memory owned by the ctx, in bytes. */
+long long insb200_workspace_bytes(const insb200_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* INSB200_H */

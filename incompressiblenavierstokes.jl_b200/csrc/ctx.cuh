@@ -1,0 +1,189 @@
+// ctx.cuh -- context, views and error plumbing of libinsb200 (sm_100a).
+//
+// Data layout in HBM
+//   reference layout ("ghosted"): what the Julia caller owns, column-major (N1,..,ND[,D]),
+//     N_a = nloc_a + 2 (src/grid.jl:121).  Row pitch (n+2)*sizeof(T) is NOT a multiple of 16 B in
+//     Float32, so rows are neither float4- nor TMA-addressable.
+//   compact layout (internal): interior cells only, x/y periodic by index wrap, the last axis
+//     either wrapped (nranks == 1) or padded with G ghost planes filled over NCCL (nranks > 1).
+//     Row pitch n*sizeof(T) is a multiple of 16 B for every admissible n (n even and, for the
+//     vector paths, n % 4 == 0), so rows can be moved with 128-bit loads / bulk copies.
+//   The RK state (ustart, stage buffers, k_i, sigma, FFT buffers) lives in the compact layout;
+//   the reference layout is touched once on entry and once on exit of a stepping call.
+#pragma once
+#include <cuda_runtime.h>
+#include <cufft.h>
+#include <nccl.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/insb200.h"
+
+namespace insb200 {
+
+typedef long long i64;
+
+// A field view: pointer to cell (0,0,0) of component 0 of the INTERIOR, strides in elements.
+template <typename T>
+struct View {
+  T *p;
+  i64 sy, sz, sc;  // x stride is 1
+};
+
+// Local geometry handed to kernels.
+struct Geo {
+  int n[3];     // local interior cells per axis (n[2] = 1 in 2-D)
+  int wrap[3];  // 1: periodic wrap by index (compact layout); 0: ghost cells are addressable
+};
+
+enum TimerId {
+  TM_IMPORT = 0, TM_EXPORT, TM_BC, TM_MOMENTUM, TM_STAGE, TM_SMAGTENSOR, TM_DIVTENSOR, TM_DIVERGENCE,
+  TM_FFT_FWD, TM_FFT_INV, TM_POISSON_SCALE, TM_GRADIENT, TM_REDUCE, TM_HALO, TM_PACK, TM_A2A,
+  TM_MISC, TM_COUNT
+};
+static const char *const kTimerNames[TM_COUNT] = {
+    "import_ghosted", "export_ghosted", "apply_bc", "momentum", "momentum_stage", "smagtensor",
+    "divoftensor", "divergence", "cufft_forward", "cufft_inverse", "poisson_scale", "pressure_gradient",
+    "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc"};
+
+struct TimerRec {
+  cudaEvent_t a, b;
+  int id;
+};
+
+}  // namespace insb200
+
+struct insb200_ctx {
+  int D = 0;
+  int dtype = 0;           // 0 f32, 1 f64
+  int nglob[3] = {1, 1, 1};
+  int nloc[3] = {1, 1, 1};
+  int last = 0;            // index of the decomposed (last) axis
+  int off_last = 0;        // first global plane of this rank on the last axis
+  double h[3] = {1, 1, 1};
+  double Re = 1;
+  int device = 0;
+  int rank = 0, nranks = 1;
+  int variant = 1;
+  cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;
+  ncclComm_t comm = nullptr;
+  std::string err;
+
+  // compact-layout geometry
+  int G = 0;               // ghost planes on the last axis of compact vector buffers (0 if nranks==1)
+  insb200::i64 csy = 0, csz = 0;      // compact strides
+  insb200::i64 cplane = 0;            // elements of one last-axis plane
+  insb200::i64 ccomp = 0;             // elements per component incl. ghost planes
+  insb200::i64 cint = 0;              // interior elements per component
+
+  // workspaces (device), element type = dtype
+  void *ubuf[3] = {nullptr, nullptr, nullptr};          // rotating state buffers (compact vector)
+  void *kbuf[INSB200_MAX_STAGES] = {nullptr};           // stage derivatives
+  void *force = nullptr;                                // compact steady body force (nullable)
+  void *sigma = nullptr;                                // compact symmetric tensor, D(D+1)/2 comps
+  void *preal = nullptr;                                // compact scalar: FFT real buffer (+ ghost planes)
+  void *pcplx = nullptr;                                // complex spectrum
+  void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
+  void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)
+  void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)
+  void *hostio = nullptr;                               // reference-layout device image for *_host calls
+  void *red = nullptr;                                  // reduction partials (double)
+  double *red_host = nullptr;                           // pinned
+  void *cufft_work = nullptr;
+  size_t cufft_work_bytes = 0;
+  insb200::i64 ws_bytes = 0;
+  bool rk_alloc = false;
+  int rk_nk = 0;
+
+  // FFT plans
+  cufftHandle plan_fwd = 0, plan_inv = 0;               // nranks==1: D-dim R2C / C2R
+  cufftHandle plan_fwd_in = 0, plan_inv_in = 0;         // nranks>1: in-slab transforms
+  cufftHandle plan_last = 0;                            // nranks>1: C2C along the last axis
+  bool plans = false;
+  int nxh = 0;                                          // n[0]/2+1
+  int kxc = 0, kx0 = 0, kxl = 0;                        // kx chunk size, my first kx, my kx count
+
+  // accounting
+  long long launches = 0, fft_execs = 0;
+  bool profiling = false;
+  std::vector<insb200::TimerRec> recs;
+  std::vector<cudaEvent_t> pool;
+  double tm_ms[insb200::TM_COUNT] = {0};
+  long long tm_cnt[insb200::TM_COUNT] = {0};
+};
+
+namespace insb200 {
+
+extern thread_local std::string g_create_error;
+
+inline int fail(insb200_ctx *c, const char *file, int line, const std::string &msg) {
+  char buf[96];
+  const char *base = strrchr(file, '/');
+  snprintf(buf, sizeof buf, " [%s:%d]", base ? base + 1 : file, line);
+  std::string m = msg + buf;
+  if (c) c->err = m; else g_create_error = m;
+  return 1;
+}
+
+#define INS_FAIL(ctx, msg) return ::insb200::fail((ctx), __FILE__, __LINE__, (msg))
+#define INS_CUDA(ctx, call)                                                                     \
+  do {                                                                                          \
+    cudaError_t e_ = (call);                                                                    \
+    if (e_ != cudaSuccess)                                                                      \
+      return ::insb200::fail((ctx), __FILE__, __LINE__, std::string("CUDA: ") + cudaGetErrorString(e_) + " in " #call); \
+  } while (0)
+#define INS_CUFFT(ctx, call)                                                                    \
+  do {                                                                                          \
+    cufftResult r_ = (call);                                                                    \
+    if (r_ != CUFFT_SUCCESS)                                                                    \
+      return ::insb200::fail((ctx), __FILE__, __LINE__, std::string("cuFFT error ") + std::to_string((int)r_) + " in " #call); \
+  } while (0)
+#define INS_NCCL(ctx, call)                                                                     \
+  do {                                                                                          \
+    ncclResult_t r_ = (call);                                                                   \
+    if (r_ != ncclSuccess)                                                                      \
+      return ::insb200::fail((ctx), __FILE__, __LINE__, std::string("NCCL: ") + ncclGetErrorString(r_) + " in " #call); \
+  } while (0)
+#define INS_TRY(call)            \
+  do {                           \
+    int r__ = (call);            \
+    if (r__) return r__;         \
+  } while (0)
+
+// scoped device timer: records an event pair around the launches of one logical kernel
+struct ScopedTimer {
+  insb200_ctx *c;
+  int id;
+  cudaEvent_t a = nullptr, b = nullptr;
+  ScopedTimer(insb200_ctx *c_, int id_) : c(c_), id(id_) {
+    if (!c->profiling) return;
+    a = take();
+    b = take();
+    cudaEventRecord(a, c->stream);
+  }
+  ~ScopedTimer() {
+    if (!c->profiling) return;
+    cudaEventRecord(b, c->stream);
+    c->recs.push_back({a, b, id});
+  }
+  cudaEvent_t take() {
+    if (!c->pool.empty()) {
+      cudaEvent_t e = c->pool.back();
+      c->pool.pop_back();
+      return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+  }
+};
+
+inline size_t esize(const insb200_ctx *c) { return c->dtype == INSB200_F64 ? 8 : 4; }
+
+}  // namespace insb200

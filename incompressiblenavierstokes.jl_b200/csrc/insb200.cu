@@ -1,0 +1,1070 @@
+// insb200.cu -- C ABI (include/insb200.h) and host orchestration of the B200 time-stepping core.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -fmad=false ... (see build.py)
+//
+// No CPU fallback exists anywhere in this file: every operator is a CUDA kernel launch (own
+// kernels + cuFFT for the transforms + NCCL for halos / the FFT transpose).
+#include <algorithm>
+#include <limits>
+#include <type_traits>
+
+#include "ctx.cuh"
+#include "stencil.cuh"
+#include "tiled.cuh"
+
+namespace insb200 {
+thread_local std::string g_create_error;
+
+static const int kG = 1;  // ghost planes on the decomposed axis of compact buffers (nranks > 1)
+
+// ---- small host helpers ------------------------------------------------------------------------
+static inline dim3 cell_block() { return dim3(64, 4, 1); }
+static inline dim3 cell_grid(const int n[3]) {
+  return dim3((n[0] + 63) / 64, (n[1] + 3) / 4, n[2]);
+}
+
+static Geo geo_ghosted(const insb200_ctx *c) {
+  Geo g;
+  for (int d = 0; d < 3; d++) { g.n[d] = c->nloc[d]; g.wrap[d] = 0; }
+  return g;
+}
+static Geo geo_compact(const insb200_ctx *c) {
+  Geo g;
+  for (int d = 0; d < 3; d++) { g.n[d] = c->nloc[d]; g.wrap[d] = 1; }
+  if (c->nranks > 1) g.wrap[c->last] = 0;
+  return g;
+}
+
+// reference-layout view of a caller array
+template <typename T>
+static View<T> view_ghosted(const insb200_ctx *c, void *base) {
+  View<T> v;
+  const i64 N0 = c->nloc[0] + 2, N1 = c->nloc[1] + 2, N2 = c->D == 3 ? c->nloc[2] + 2 : 1;
+  v.sy = N0;
+  v.sz = c->D == 3 ? N0 * N1 : 0;
+  v.sc = N0 * N1 * N2;
+  v.p = (T *)base + 1 + v.sy + v.sz;
+  return v;
+}
+template <typename T>
+static View<const T> view_ghosted_c(const insb200_ctx *c, const void *base) {
+  View<T> v = view_ghosted<T>(c, const_cast<void *>(base));
+  return View<const T>{v.p, v.sy, v.sz, v.sc};
+}
+// compact view of an internal buffer (vector, scalar or tensor: sc is the same for all)
+template <typename T>
+static View<T> view_compact(const insb200_ctx *c, void *base) {
+  View<T> v;
+  v.sy = c->csy;
+  v.sz = c->csz;
+  v.sc = c->ccomp;
+  v.p = (T *)base + (i64)c->G * c->cplane;
+  return v;
+}
+template <typename T>
+static View<const T> view_compact_c(const insb200_ctx *c, const void *base) {
+  View<T> v = view_compact<T>(c, const_cast<void *>(base));
+  return View<const T>{v.p, v.sy, v.sz, v.sc};
+}
+
+template <typename T>
+static Rh<T> make_rh(const insb200_ctx *c) {
+  Rh<T> r;
+  for (int d = 0; d < 3; d++) r.v[d] = T(1) / T(c->h[d]);
+  return r;
+}
+template <typename T>
+static T volume(const insb200_ctx *c) {  // (dx*dy)*dz in T  (operators.jl:92)
+  T v = T(c->h[0]) * T(c->h[1]);
+  if (c->D == 3) v = v * T(c->h[2]);
+  return v;
+}
+
+static int dev_alloc(insb200_ctx *c, void **p, size_t bytes) {
+  if (*p) return 0;
+  INS_CUDA(c, cudaMalloc(p, bytes));
+  INS_CUDA(c, cudaMemsetAsync(*p, 0, bytes, c->stream));
+  c->ws_bytes += (i64)bytes;
+  return 0;
+}
+
+static double sinpi01(double x) {  // x in [0,1]; reduced so that multiples of 1/2 are exact
+  double r = x > 0.5 ? 1.0 - x : x;
+  return std::sin(M_PI * r);
+}
+
+#define DISPATCH(c, FN, ...)                                                           \
+  ((c)->dtype == INSB200_F32 ? ((c)->D == 2 ? FN<float, 2>(__VA_ARGS__) : FN<float, 3>(__VA_ARGS__)) \
+                             : ((c)->D == 2 ? FN<double, 2>(__VA_ARGS__) : FN<double, 3>(__VA_ARGS__)))
+
+#define CHECK_LAUNCH(c)                      \
+  do {                                       \
+    (c)->launches++;                         \
+    INS_CUDA((c), cudaGetLastError());       \
+  } while (0)
+
+#define CHECK_CTX(c) \
+  if (!(c)) return 1; \
+  if (cudaSetDevice((c)->device) != cudaSuccess) INS_FAIL((c), "cudaSetDevice failed")
+
+// ---- halo exchange along the decomposed axis (nranks > 1) ---------------------------------------
+// compact buffer with kG ghost planes each side; ncomp components of stride ccomp.
+// minus: fill my bottom ghost from prev's top interior plane; plus: my top ghost from next's bottom.
+template <typename T>
+static int halo_compact(insb200_ctx *c, void *base, int ncomp, bool minus, bool plus) {
+  if (c->nranks == 1) return 0;
+  ScopedTimer tm(c, TM_HALO);
+  const int prev = (c->rank + c->nranks - 1) % c->nranks, next = (c->rank + 1) % c->nranks;
+  const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
+  const i64 pl = c->cplane, nl = c->nloc[c->last];
+  INS_NCCL(c, ncclGroupStart());
+  for (int q = 0; q < ncomp; q++) {
+    T *b = (T *)base + q * c->ccomp;
+    if (minus) {  // top interior plane -> next ; recv bottom ghost <- prev
+      INS_NCCL(c, ncclSend(b + (kG + nl - 1) * pl, pl, dt, next, c->comm, c->stream));
+      INS_NCCL(c, ncclRecv(b + (kG - 1) * pl, pl, dt, prev, c->comm, c->stream));
+    }
+    if (plus) {  // bottom interior plane -> prev ; recv top ghost <- next
+      INS_NCCL(c, ncclSend(b + kG * pl, pl, dt, prev, c->comm, c->stream));
+      INS_NCCL(c, ncclRecv(b + (kG + nl) * pl, pl, dt, next, c->comm, c->stream));
+    }
+  }
+  INS_NCCL(c, ncclGroupEnd());
+  return 0;
+}
+
+}  // namespace insb200
+using namespace insb200;
+
+// =================================================================================================
+// life cycle
+// =================================================================================================
+extern "C" int insb200_version(void) { return 100; }
+
+extern "C" int insb200_comm_unique_id(void *id128) {
+  static_assert(sizeof(ncclUniqueId) <= INSB200_NCCL_ID_BYTES, "id size");
+  ncclUniqueId id;
+  if (ncclGetUniqueId(&id) != ncclSuccess) { g_create_error = "ncclGetUniqueId failed"; return 1; }
+  memset(id128, 0, INSB200_NCCL_ID_BYTES);
+  memcpy(id128, &id, sizeof id);
+  return 0;
+}
+
+template <typename T>
+static int upload_symbol(insb200_ctx *c) {
+  // ahat[a][k] = 4*Omega*sinpi(k/n_a)^2 / dx_a^2, evaluated in Float64 and stored as T
+  // (src/pressure.jl:305-311: k/Np is Float64; Omega = prod(dx) and dx^2 are formed in T)
+  T om = T(c->h[0]);
+  for (int a = 1; a < c->D; a++) om = om * T(c->h[a]);
+  for (int a = 0; a < c->D; a++) {
+    const int n = c->nglob[a];
+    const int kmax = a == 0 ? n / 2 + 1 : n;
+    std::vector<T> v(kmax);
+    const T dx = T(c->h[a]);
+    const double num = (double)(T(4) * om), den = (double)(dx * dx);
+    for (int k = 0; k < kmax; k++) {
+      const double s = sinpi01((double)k / (double)n);
+      v[k] = (T)(num * (s * s) / den);
+    }
+    INS_TRY(dev_alloc(c, &c->ahat[a], kmax * sizeof(T)));
+    INS_CUDA(c, cudaMemcpyAsync(c->ahat[a], v.data(), kmax * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  return 0;
+}
+
+extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype, const double *h, double Re,
+                              int device, int rank, int nranks, const void *nccl_id) {
+  if (!out) { g_create_error = "ctx output pointer is NULL"; return 1; }
+  *out = nullptr;
+  if (D != 2 && D != 3) INS_FAIL(nullptr, "D must be 2 or 3");
+  if (dtype != INSB200_F32 && dtype != INSB200_F64) INS_FAIL(nullptr, "dtype must be 0 (Float32) or 1 (Float64)");
+  if (nranks < 1 || rank < 0 || rank >= nranks) INS_FAIL(nullptr, "bad rank / nranks");
+  for (int a = 0; a < D; a++) {
+    if (n[a] < 2 || (n[a] & 1)) INS_FAIL(nullptr, "spectral pressure solver requires an even number of volumes >= 2 per axis (utils.jl:10-12)");
+    if (!(h[a] > 0)) INS_FAIL(nullptr, "grid spacing must be positive");
+  }
+  if (!(Re > 0)) INS_FAIL(nullptr, "Re must be positive");
+  if (n[D - 1] % nranks) INS_FAIL(nullptr, "the last axis must be divisible by the number of ranks");
+  if (nranks > 1 && n[D - 1] / nranks < 2) INS_FAIL(nullptr, "each rank needs at least 2 planes");
+  if (nranks > 1 && !nccl_id) INS_FAIL(nullptr, "nccl_id required when nranks > 1");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    INS_FAIL(nullptr, "no CUDA device available: libinsb200 has no CPU fallback");
+  if (device < 0 || device >= ndev) INS_FAIL(nullptr, "bad device ordinal");
+
+  insb200_ctx *c = new insb200_ctx();
+  c->D = D; c->dtype = dtype; c->Re = Re; c->device = device; c->rank = rank; c->nranks = nranks;
+  c->last = D - 1;
+  for (int a = 0; a < D; a++) { c->nglob[a] = n[a]; c->nloc[a] = n[a]; c->h[a] = h[a]; }
+  c->nloc[c->last] = n[c->last] / nranks;
+  c->off_last = rank * c->nloc[c->last];
+  c->G = nranks > 1 ? kG : 0;
+  c->csy = c->nloc[0];
+  c->csz = D == 3 ? (i64)c->nloc[0] * c->nloc[1] : 0;
+  c->cplane = D == 3 ? c->csz : c->csy;
+  c->cint = (i64)c->nloc[0] * c->nloc[1] * c->nloc[2];
+  c->ccomp = c->cint + 2 * (i64)c->G * c->cplane;
+  c->nxh = n[0] / 2 + 1;
+  c->kxc = (c->nxh + nranks - 1) / nranks;
+  c->kx0 = std::min(rank * c->kxc, c->nxh);
+  c->kxl = std::min((rank + 1) * c->kxc, c->nxh) - c->kx0;
+
+  auto bail = [&](int r) { std::string e = c->err; insb200_destroy(c); g_create_error = e; return r; };
+  if (cudaSetDevice(device) != cudaSuccess) { c->err = "cudaSetDevice failed"; return bail(1); }
+  if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { c->err = "stream creation failed"; return bail(1); }
+  c->stream = c->own_stream;
+  if (nranks > 1) {
+    ncclUniqueId id;
+    memcpy(&id, nccl_id, sizeof id);
+    ncclResult_t r = ncclCommInitRank(&c->comm, nranks, id, rank);
+    if (r != ncclSuccess) { c->err = std::string("ncclCommInitRank: ") + ncclGetErrorString(r); return bail(1); }
+  }
+  int r = dtype == INSB200_F32 ? upload_symbol<float>(c) : upload_symbol<double>(c);
+  if (r) return bail(r);
+  // reduction scratch: partials for the largest launch + 4 outputs
+  dim3 g = cell_grid(c->nloc);
+  const i64 nb = (i64)g.x * g.y * g.z;
+  if (dev_alloc(c, &c->red, (size_t)(4 * nb + 8) * sizeof(double))) return bail(1);
+  if (cudaMallocHost((void **)&c->red_host, 8 * sizeof(double)) != cudaSuccess) { c->err = "cudaMallocHost failed"; return bail(1); }
+  *out = c;
+  return 0;
+}
+
+extern "C" int insb200_destroy(insb200_ctx *c) {
+  if (!c) return 0;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->plans) {
+    if (c->plan_fwd) cufftDestroy(c->plan_fwd);
+    if (c->plan_inv) cufftDestroy(c->plan_inv);
+    if (c->plan_fwd_in) cufftDestroy(c->plan_fwd_in);
+    if (c->plan_inv_in) cufftDestroy(c->plan_inv_in);
+    if (c->plan_last) cufftDestroy(c->plan_last);
+  }
+  for (auto &p : c->ubuf) if (p) cudaFree(p);
+  for (auto &p : c->kbuf) if (p) cudaFree(p);
+  for (auto &p : c->ahat) if (p) cudaFree(p);
+  void *ptrs[] = {c->force, c->sigma, c->preal, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  if (c->red_host) cudaFreeHost(c->red_host);
+  for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  for (auto &e : c->pool) cudaEventDestroy(e);
+  if (c->comm) ncclCommDestroy(c->comm);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  delete c;
+  return 0;
+}
+
+extern "C" const char *insb200_last_error(const insb200_ctx *c) {
+  return c ? c->err.c_str() : g_create_error.c_str();
+}
+
+extern "C" int insb200_set_stream(insb200_ctx *c, void *s) {
+  CHECK_CTX(c);
+  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  if (c->plans) {
+    cufftHandle hs[] = {c->plan_fwd, c->plan_inv, c->plan_fwd_in, c->plan_inv_in, c->plan_last};
+    for (cufftHandle hd : hs) if (hd) INS_CUFFT(c, cufftSetStream(hd, c->stream));
+  }
+  return 0;
+}
+
+extern "C" int insb200_synchronize(insb200_ctx *c) {
+  CHECK_CTX(c);
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+extern "C" int insb200_local_geometry(const insb200_ctx *c, int *nloc, int *off) {
+  if (!c) return 1;
+  for (int a = 0; a < c->D; a++) nloc[a] = c->nloc[a];
+  if (off) *off = c->off_last;
+  return 0;
+}
+
+// =================================================================================================
+// lazily created workspaces and plans
+// =================================================================================================
+namespace insb200 {
+
+static int ensure_fft(insb200_ctx *c) {
+  if (c->plans) return 0;
+  const size_t es = esize(c);
+  const int D = c->D;
+  const bool f32 = c->dtype == INSB200_F32;
+  // real buffer: interior + ghost planes on the decomposed axis (the gradient reads p[I+e])
+  INS_TRY(dev_alloc(c, &c->preal, (size_t)c->ccomp * es));
+  if (c->nranks == 1) {
+    const i64 nc = (i64)c->nxh * c->nloc[1] * c->nloc[2];
+    INS_TRY(dev_alloc(c, &c->pcplx, (size_t)nc * 2 * es));
+    if (D == 2) {
+      INS_CUFFT(c, cufftPlan2d(&c->plan_fwd, c->nloc[1], c->nloc[0], f32 ? CUFFT_R2C : CUFFT_D2Z));
+      INS_CUFFT(c, cufftPlan2d(&c->plan_inv, c->nloc[1], c->nloc[0], f32 ? CUFFT_C2R : CUFFT_Z2D));
+    } else {
+      INS_CUFFT(c, cufftPlan3d(&c->plan_fwd, c->nloc[2], c->nloc[1], c->nloc[0], f32 ? CUFFT_R2C : CUFFT_D2Z));
+      INS_CUFFT(c, cufftPlan3d(&c->plan_inv, c->nloc[2], c->nloc[1], c->nloc[0], f32 ? CUFFT_C2R : CUFFT_Z2D));
+    }
+    INS_CUFFT(c, cufftSetStream(c->plan_fwd, c->stream));
+    INS_CUFFT(c, cufftSetStream(c->plan_inv, c->stream));
+  } else {
+    // rows of the in-slab spectrum: 3-D: ny*nzl, 2-D: nyl
+    const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
+    const i64 slots = (i64)c->nranks * c->kxc * rows;  // >= rows*nxh and >= nranks*rows*kxl
+    INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
+    INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
+    if (D == 3) {
+      int nn[2] = {c->nloc[1], c->nloc[0]};
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
+    } else {
+      int nn[1] = {c->nloc[0]};
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 1, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[1]));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 1, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[1]));
+    }
+    INS_CUFFT(c, cufftSetStream(c->plan_fwd_in, c->stream));
+    INS_CUFFT(c, cufftSetStream(c->plan_inv_in, c->stream));
+    if (c->kxl > 0) {
+      // transposed spectrum (kxl fastest, ky, z-global): transform along the last axis
+      int nn[1] = {c->nglob[c->last]};
+      const int stride = D == 3 ? c->kxl * c->nglob[1] : c->kxl;
+      int emb[1] = {c->nglob[c->last]};
+      INS_CUFFT(c, cufftPlanMany(&c->plan_last, 1, nn, emb, stride, 1, emb, stride, 1, f32 ? CUFFT_C2C : CUFFT_Z2Z, stride));
+      INS_CUFFT(c, cufftSetStream(c->plan_last, c->stream));
+    }
+  }
+  c->plans = true;
+  return 0;
+}
+
+static int ensure_vec(insb200_ctx *c, void **p) { return dev_alloc(c, p, (size_t)c->ccomp * c->D * esize(c)); }
+static int ensure_sigma(insb200_ctx *c) {
+  return dev_alloc(c, &c->sigma, (size_t)c->ccomp * (c->D * (c->D + 1) / 2) * esize(c));
+}
+
+// ---- layout conversion ----------------------------------------------------------------------------
+template <typename T, int D>
+static int import_field(insb200_ctx *c, void *compact, const void *ghosted, int nc) {
+  ScopedTimer tm(c, TM_IMPORT);
+  Geo g = geo_ghosted(c);
+  k_copy_view<T><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_compact<T>(c, compact), view_ghosted_c<T>(c, ghosted), g, nc);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+template <typename T, int D>
+static int export_field(insb200_ctx *c, void *ghosted, const void *compact, int nc) {
+  ScopedTimer tm(c, TM_EXPORT);
+  Geo g = geo_ghosted(c);
+  k_copy_view<T><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_ghosted<T>(c, ghosted), view_compact_c<T>(c, compact), g, nc);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// periodic ghost fill of a reference-layout array with nc components (apply_bc_u! / apply_bc_p!)
+template <typename T, int D>
+static int bc_fill(insb200_ctx *c, void *base, int nc) {
+  ScopedTimer tm(c, TM_BC);
+  View<T> v = view_ghosted<T>(c, base);
+  const int skip = c->nranks > 1 ? c->last : -1;
+  for (int axis = 0; axis < D; axis++) {
+    if (axis == skip) continue;
+    const int o0 = axis == 0 ? 1 : 0;
+    const int o1 = D == 3 ? (axis == 2 ? 1 : 2) : -1;
+    dim3 blk(128, D == 3 ? 2 : 1, 1);
+    dim3 grd((c->nloc[o0] + 2 + 127) / 128, D == 3 ? (c->nloc[o1] + 2 + 1) / 2 : 1, 2 * nc);
+    k_bc_axis<T><<<grd, blk, 0, c->stream>>>(v.p, v.sy, v.sz, v.sc, c->nloc[0], c->nloc[1], c->nloc[2], D, nc, axis, skip);
+    CHECK_LAUNCH(c);
+  }
+  if (c->nranks > 1) {
+    // ghost planes of the decomposed axis: full planes (x/y ghosts included) from the ring neighbours
+    const int prev = (c->rank + c->nranks - 1) % c->nranks, next = (c->rank + 1) % c->nranks;
+    const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
+    const i64 pl = D == 3 ? (i64)(c->nloc[0] + 2) * (c->nloc[1] + 2) : (c->nloc[0] + 2);
+    const i64 nl = c->nloc[c->last];
+    INS_NCCL(c, ncclGroupStart());
+    for (int q = 0; q < nc; q++) {
+      T *b = (T *)base + q * v.sc;
+      INS_NCCL(c, ncclSend(b + nl * pl, pl, dt, next, c->comm, c->stream));        // last interior plane
+      INS_NCCL(c, ncclRecv(b, pl, dt, prev, c->comm, c->stream));                  // ghost plane 0
+      INS_NCCL(c, ncclSend(b + pl, pl, dt, prev, c->comm, c->stream));             // first interior plane
+      INS_NCCL(c, ncclRecv(b + (nl + 1) * pl, pl, dt, next, c->comm, c->stream));  // ghost plane N-1
+    }
+    INS_NCCL(c, ncclGroupEnd());
+  }
+  return 0;
+}
+
+// ---- spectral Poisson solve on the compact real buffer (in: preal interior = rhs; out: solution) --
+template <typename T, int D>
+static int poisson_solve(insb200_ctx *c) {
+  INS_TRY(ensure_fft(c));
+  typedef typename std::conditional<sizeof(T) == 4, cufftComplex, cufftDoubleComplex>::type C;
+  T *pr = (T *)c->preal + (i64)c->G * c->cplane;
+  C *S = (C *)c->pcplx;
+  const double ntot = (double)c->nglob[0] * c->nglob[1] * (D == 3 ? c->nglob[2] : 1);
+  const T invN = T(1) / T(ntot);
+  if (c->nranks == 1) {
+    {
+      ScopedTimer tm(c, TM_FFT_FWD);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd, (cufftReal *)pr, (cufftComplex *)S));
+      else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
+      c->fft_execs++;
+    }
+    {
+      ScopedTimer tm(c, TM_POISSON_SCALE);
+      dim3 blk(64, 4, 1), grd((c->nxh + 63) / 64, (c->nloc[1] + 3) / 4, c->nloc[2]);
+      k_poisson_scale<T, C, D><<<grd, blk, 0, c->stream>>>(S, (const T *)c->ahat[0], (const T *)c->ahat[1], (const T *)c->ahat[2],
+                                                         c->nxh, c->nloc[1], c->nloc[2], 0, invN);
+      CHECK_LAUNCH(c);
+    }
+    {
+      ScopedTimer tm(c, TM_FFT_INV);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv, (cufftComplex *)S, (cufftReal *)pr));
+      else INS_CUFFT(c, cufftExecZ2D(c->plan_inv, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
+      c->fft_execs++;
+    }
+    return 0;
+  }
+  // ---- slab-decomposed transform: in-slab FFT -> pack -> all-to-all -> last-axis FFT -> scale -> back
+  C *B = (C *)c->pcplx2;
+  const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
+  const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
+  auto chunk_w = [&](int q) { return std::max(0, std::min((q + 1) * c->kxc, c->nxh) - q * c->kxc); };
+  dim3 pblk(64, 4, 1), pgrd((unsigned)((rows + 3) / 4), (c->nxh + 63) / 64, 1);
+  {
+    ScopedTimer tm(c, TM_FFT_FWD);
+    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)pr, (cufftComplex *)S));
+    else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
+    c->fft_execs++;
+  }
+  {
+    ScopedTimer tm(c, TM_PACK);
+    k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 0);
+    CHECK_LAUNCH(c);
+  }
+  {
+    ScopedTimer tm(c, TM_A2A);
+    INS_NCCL(c, ncclGroupStart());
+    for (int q = 0; q < c->nranks; q++) {
+      const i64 ns = rows * chunk_w(q) * 2, nr = rows * c->kxl * 2;
+      if (ns) INS_NCCL(c, ncclSend((T *)(B + (i64)q * c->kxc * rows), ns, dt, q, c->comm, c->stream));
+      if (nr) INS_NCCL(c, ncclRecv((T *)(S + (i64)q * rows * c->kxl), nr, dt, q, c->comm, c->stream));
+    }
+    INS_NCCL(c, ncclGroupEnd());
+  }
+  if (c->kxl > 0) {
+    {
+      ScopedTimer tm(c, TM_FFT_FWD);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)S, (cufftComplex *)S, CUFFT_FORWARD));
+      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)S, (cufftDoubleComplex *)S, CUFFT_FORWARD));
+      c->fft_execs++;
+    }
+    {
+      ScopedTimer tm(c, TM_POISSON_SCALE);
+      // layout (kxl fastest, ky, kz) in 3-D; (kxl fastest, ky) in 2-D
+      const int nky = c->nglob[1], nkz = D == 3 ? c->nglob[2] : 1;
+      dim3 blk(64, 4, 1), grd((c->kxl + 63) / 64, (nky + 3) / 4, nkz);
+      k_poisson_scale<T, C, D><<<grd, blk, 0, c->stream>>>(S, (const T *)c->ahat[0], (const T *)c->ahat[1], (const T *)c->ahat[2],
+                                                         c->kxl, nky, nkz, c->kx0, invN);
+      CHECK_LAUNCH(c);
+    }
+    {
+      ScopedTimer tm(c, TM_FFT_INV);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)S, (cufftComplex *)S, CUFFT_INVERSE));
+      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)S, (cufftDoubleComplex *)S, CUFFT_INVERSE));
+      c->fft_execs++;
+    }
+  }
+  {
+    ScopedTimer tm(c, TM_A2A);
+    INS_NCCL(c, ncclGroupStart());
+    for (int q = 0; q < c->nranks; q++) {
+      const i64 ns = rows * c->kxl * 2, nr = rows * chunk_w(q) * 2;
+      if (ns) INS_NCCL(c, ncclSend((T *)(S + (i64)q * rows * c->kxl), ns, dt, q, c->comm, c->stream));
+      if (nr) INS_NCCL(c, ncclRecv((T *)(B + (i64)q * c->kxc * rows), nr, dt, q, c->comm, c->stream));
+    }
+    INS_NCCL(c, ncclGroupEnd());
+  }
+  {
+    ScopedTimer tm(c, TM_PACK);
+    k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 1);
+    CHECK_LAUNCH(c);
+  }
+  {
+    ScopedTimer tm(c, TM_FFT_INV);
+    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
+    else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
+    c->fft_execs++;
+  }
+  return 0;
+}
+
+}  // namespace insb200
+
+// =================================================================================================
+// operators on reference-layout device fields
+// =================================================================================================
+namespace insb200 {
+
+template <typename T, int D>
+static int op_apply_bc(insb200_ctx *c, void *f, int nc) { return bc_fill<T, D>(c, f, nc); }
+
+template <typename T, int D>
+static int op_set_bodyforce(insb200_ctx *c, const void *f) {
+  INS_TRY(ensure_vec(c, &c->force));
+  return import_field<T, D>(c, c->force, f, D);
+}
+
+// F = convdiff(u) [+ force], written to any view
+template <typename T, int D>
+static int launch_momentum(insb200_ctx *c, View<T> F, View<const T> u, Geo g, int terms, bool with_force) {
+  ScopedTimer tm(c, TM_MOMENTUM);
+  const T visc = T(1) / T(c->Re);
+  View<const T> fv{nullptr, 0, 0, 0};
+  if (with_force && c->force) fv = view_compact_c<T>(c, c->force);
+  dim3 grd = cell_grid(c->nloc), blk = cell_block();
+  Rh<T> rh = make_rh<T>(c);
+  if (terms == 3) k_momentum<T, D, true, true><<<grd, blk, 0, c->stream>>>(F, u, fv, g, visc, rh);
+  else if (terms == 1) k_momentum<T, D, true, false><<<grd, blk, 0, c->stream>>>(F, u, fv, g, visc, rh);
+  else k_momentum<T, D, false, true><<<grd, blk, 0, c->stream>>>(F, u, fv, g, visc, rh);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+static i64 ghosted_elems(const insb200_ctx *c) {
+  i64 e = 1;
+  for (int a = 0; a < c->D; a++) e *= c->nloc[a] + 2;
+  return e;
+}
+
+template <typename T, int D>
+static int op_momentum(insb200_ctx *c, void *F, const void *u, int terms, bool with_force) {
+  // fill!(F, 0): ghosts of F stay zero (operators.jl:971)
+  INS_CUDA(c, cudaMemsetAsync(F, 0, (size_t)ghosted_elems(c) * D * sizeof(T), c->stream));
+  return launch_momentum<T, D>(c, view_ghosted<T>(c, F), view_ghosted_c<T>(c, u), geo_ghosted(c), terms, with_force);
+}
+
+template <typename T>
+static T eddy_const(const insb200_ctx *c, double theta) {
+  // theta^2 * d^2 with d = sqrt(sum h_a^2)  (operators.jl:1128, 1146)
+  T s = T(0);
+  for (int a = 0; a < c->D; a++) s = (a == 0) ? T(c->h[a]) * T(c->h[a]) : s + T(c->h[a]) * T(c->h[a]);
+  const T d = std::sqrt(s);
+  const T th = T(theta);
+  return (th * th) * (d * d);
+}
+
+// sigma(u) on all local p-cells into c->sigma, then its halo on the decomposed axis
+template <typename T, int D>
+static int compute_sigma(insb200_ctx *c, View<const T> u, Geo gu, double theta) {
+  INS_TRY(ensure_sigma(c));
+  {
+    ScopedTimer tm(c, TM_SMAGTENSOR);
+    k_smagtensor<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_compact<T>(c, c->sigma), u, gu,
+                                                                        eddy_const<T>(c, theta), make_rh<T>(c));
+    CHECK_LAUNCH(c);
+  }
+  return halo_compact<T>(c, c->sigma, D * (D + 1) / 2, true, true);
+}
+
+template <typename T, int D>
+static int op_smagorinsky(insb200_ctx *c, void *s, const void *u, double theta) {
+  INS_TRY((compute_sigma<T, D>(c, view_ghosted_c<T>(c, u), geo_ghosted(c), theta)));
+  INS_CUDA(c, cudaMemsetAsync(s, 0, (size_t)ghosted_elems(c) * D * sizeof(T), c->stream));
+  ScopedTimer tm(c, TM_DIVTENSOR);
+  k_divtensor<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_ghosted<T>(c, s), view_compact_c<T>(c, c->sigma),
+                                                                     geo_compact(c), make_rh<T>(c));
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D>
+static int launch_divergence(insb200_ctx *c, View<T> out, View<const T> u, Geo g, bool scale) {
+  ScopedTimer tm(c, TM_DIVERGENCE);
+  k_divergence<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(out, u, g, make_rh<T>(c), volume<T>(c), scale ? 1 : 0);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D>
+static int op_divergence(insb200_ctx *c, void *div, const void *u) {
+  View<T> o = view_ghosted<T>(c, div);
+  return launch_divergence<T, D>(c, o, view_ghosted_c<T>(c, u), geo_ghosted(c), false);
+}
+
+template <typename T, int D>
+static int op_scalewithvolume(insb200_ctx *c, void *p) {
+  ScopedTimer tm(c, TM_MISC);
+  const i64 n = ghosted_elems(c);
+  k_scale<T><<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>((T *)p, n, volume<T>(c));
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D, int MODE>
+static int launch_gradient(insb200_ctx *c, View<T> out, View<const T> p, Geo gp) {
+  ScopedTimer tm(c, TM_GRADIENT);
+  k_gradient<T, D, MODE><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D>
+static int op_pressuregradient(insb200_ctx *c, void *G, const void *p) {
+  View<const T> pv = view_ghosted_c<T>(c, p);
+  return launch_gradient<T, D, 0>(c, view_ghosted<T>(c, G), pv, geo_ghosted(c));
+}
+template <typename T, int D>
+static int op_applypressure(insb200_ctx *c, void *u, const void *p) {
+  View<const T> pv = view_ghosted_c<T>(c, p);
+  return launch_gradient<T, D, 1>(c, view_ghosted<T>(c, u), pv, geo_ghosted(c));
+}
+
+template <typename T, int D>
+static int op_psolve(insb200_ctx *c, void *p) {
+  INS_TRY(ensure_fft(c));
+  INS_TRY((import_field<T, D>(c, c->preal, p, 1)));
+  INS_TRY((poisson_solve<T, D>(c)));
+  return export_field<T, D>(c, p, c->preal, 1);
+}
+
+// project on any view of u (reference layout or compact): divergence*Omega -> solve -> u -= grad p
+template <typename T, int D>
+static int project_view(insb200_ctx *c, View<T> u, Geo gu) {
+  INS_TRY(ensure_fft(c));
+  View<const T> uc{u.p, u.sy, u.sz, u.sc};
+  INS_TRY((launch_divergence<T, D>(c, view_compact<T>(c, c->preal), uc, gu, true)));
+  INS_TRY((poisson_solve<T, D>(c)));
+  INS_TRY((halo_compact<T>(c, c->preal, 1, false, true)));
+  return launch_gradient<T, D, 1>(c, u, view_compact_c<T>(c, c->preal), geo_compact(c));
+}
+
+template <typename T, int D>
+static int export_p(insb200_ctx *c, void *p) {
+  INS_TRY((export_field<T, D>(c, p, c->preal, 1)));
+  return bc_fill<T, D>(c, p, 1);
+}
+
+template <typename T, int D>
+static int op_project(insb200_ctx *c, void *u, void *p) {
+  INS_TRY((project_view<T, D>(c, view_ghosted<T>(c, u), geo_ghosted(c))));
+  if (p) INS_TRY((export_p<T, D>(c, p)));
+  return 0;
+}
+
+template <typename T, int D>
+static int op_pressure(insb200_ctx *c, void *p, const void *u) {
+  INS_TRY(ensure_fft(c));
+  INS_TRY(ensure_vec(c, &c->fwork));
+  // momentum!(F,u) -> apply_bc_u!(F; dudt) (periodic: wrap / halo) -> divergence -> scale -> solve -> bc
+  INS_TRY((launch_momentum<T, D>(c, view_compact<T>(c, c->fwork), view_ghosted_c<T>(c, u), geo_ghosted(c), 3, true)));
+  INS_TRY((halo_compact<T>(c, c->fwork, D, true, false)));
+  INS_TRY((launch_divergence<T, D>(c, view_compact<T>(c, c->preal), view_compact_c<T>(c, c->fwork), geo_compact(c), true)));
+  INS_TRY((poisson_solve<T, D>(c)));
+  return export_p<T, D>(c, p);
+}
+
+// ---- reductions ---------------------------------------------------------------------------------
+// out (host, 4 doubles): [0] kinetic energy sum, [1..3] max |u_a|  -- over all ranks
+template <typename T, int D>
+static int reduce_view(insb200_ctx *c, View<const T> u, Geo g, double *out4) {
+  {
+    ScopedTimer tm(c, TM_REDUCE);
+    dim3 grd = cell_grid(c->nloc);
+    const i64 nb = (i64)grd.x * grd.y * grd.z;
+    double *part_ke = (double *)c->red, *part_max = part_ke + nb, *out = part_max + 3 * nb;
+    k_reduce_partials<T, D><<<grd, cell_block(), 0, c->stream>>>(u, g, volume<T>(c), part_ke, part_max);
+    CHECK_LAUNCH(c);
+    k_reduce_final<<<1, 1024, 0, c->stream>>>(part_ke, part_max, nb, out);
+    CHECK_LAUNCH(c);
+    if (c->nranks > 1) {
+      INS_NCCL(c, ncclGroupStart());
+      INS_NCCL(c, ncclAllReduce(out, out, 1, ncclDouble, ncclSum, c->comm, c->stream));
+      INS_NCCL(c, ncclAllReduce(out + 1, out + 1, 3, ncclDouble, ncclMax, c->comm, c->stream));
+      INS_NCCL(c, ncclGroupEnd());
+    }
+    INS_CUDA(c, cudaMemcpyAsync(c->red_host, out, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+  }
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (int q = 0; q < 4; q++) out4[q] = c->red_host[q];
+  return 0;
+}
+
+// get_cfl_timestep! (solver.jl:101-125) from the per-component maxima, arithmetic in T
+template <typename T>
+static double cfl_from_max(const insb200_ctx *c, const double *out4) {
+  T dt = std::numeric_limits<T>::infinity();
+  for (int a = 0; a < c->D; a++) {
+    const T h = T(c->h[a]);
+    const T dt_diff = T(c->Re) * (h * h) / T(2);
+    const T dt_conv = h / T(out4[1 + a]);
+    dt = std::min(dt, std::min(dt_diff, dt_conv));
+  }
+  return (double)dt;
+}
+
+template <typename T, int D>
+static int op_reduce(insb200_ctx *c, const void *u, double *out4) {
+  return reduce_view<T, D>(c, view_ghosted_c<T>(c, u), geo_ghosted(c), out4);
+}
+
+}  // namespace insb200
+
+#define API_PROLOG(c) CHECK_CTX(c)
+
+extern "C" int insb200_apply_bc_u(insb200_ctx *c, void *u) {
+  API_PROLOG(c);
+  if (!u) INS_FAIL(c, "u is NULL");
+  return DISPATCH(c, op_apply_bc, c, u, c->D);
+}
+extern "C" int insb200_apply_bc_p(insb200_ctx *c, void *p) {
+  API_PROLOG(c);
+  if (!p) INS_FAIL(c, "p is NULL");
+  return DISPATCH(c, op_apply_bc, c, p, 1);
+}
+extern "C" int insb200_set_bodyforce(insb200_ctx *c, const void *f) {
+  API_PROLOG(c);
+  if (!f) {
+    if (c->force) { INS_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->force); c->force = nullptr; }
+    return 0;
+  }
+  return DISPATCH(c, op_set_bodyforce, c, f);
+}
+extern "C" int insb200_momentum(insb200_ctx *c, void *F, const void *u, double) {
+  API_PROLOG(c);
+  if (!F || !u) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_momentum, c, F, u, 3, true);
+}
+extern "C" int insb200_convectiondiffusion(insb200_ctx *c, void *F, const void *u, int terms) {
+  API_PROLOG(c);
+  if (!F || !u) INS_FAIL(c, "NULL field");
+  if (terms < 1 || terms > 3) INS_FAIL(c, "terms must be 1 (convection), 2 (diffusion) or 3 (both)");
+  return DISPATCH(c, op_momentum, c, F, u, terms, false);
+}
+extern "C" int insb200_smagorinsky(insb200_ctx *c, void *s, const void *u, double theta) {
+  API_PROLOG(c);
+  if (!s || !u) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_smagorinsky, c, s, u, theta);
+}
+extern "C" int insb200_divergence(insb200_ctx *c, void *div, const void *u) {
+  API_PROLOG(c);
+  if (!div || !u) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_divergence, c, div, u);
+}
+extern "C" int insb200_scalewithvolume(insb200_ctx *c, void *p) {
+  API_PROLOG(c);
+  if (!p) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_scalewithvolume, c, p);
+}
+extern "C" int insb200_pressuregradient(insb200_ctx *c, void *G, const void *p) {
+  API_PROLOG(c);
+  if (!G || !p) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_pressuregradient, c, G, p);
+}
+extern "C" int insb200_applypressure(insb200_ctx *c, void *u, const void *p) {
+  API_PROLOG(c);
+  if (!u || !p) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_applypressure, c, u, p);
+}
+extern "C" int insb200_psolve_spectral(insb200_ctx *c, void *p) {
+  API_PROLOG(c);
+  if (!p) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_psolve, c, p);
+}
+extern "C" int insb200_project(insb200_ctx *c, void *u, void *p) {
+  API_PROLOG(c);
+  if (!u) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_project, c, u, p);
+}
+extern "C" int insb200_pressure(insb200_ctx *c, void *p, const void *u, double) {
+  API_PROLOG(c);
+  if (!p || !u) INS_FAIL(c, "NULL field");
+  return DISPATCH(c, op_pressure, c, p, u);
+}
+extern "C" int insb200_cfl_dt(insb200_ctx *c, const void *u, double *dt) {
+  API_PROLOG(c);
+  if (!u || !dt) INS_FAIL(c, "NULL argument");
+  double o[4];
+  INS_TRY(DISPATCH(c, op_reduce, c, u, o));
+  *dt = c->dtype == INSB200_F32 ? cfl_from_max<float>(c, o) : cfl_from_max<double>(c, o);
+  return 0;
+}
+extern "C" int insb200_kinetic_energy(insb200_ctx *c, const void *u, double *E) {
+  API_PROLOG(c);
+  if (!u || !E) INS_FAIL(c, "NULL argument");
+  double o[4];
+  INS_TRY(DISPATCH(c, op_reduce, c, u, o));
+  *E = o[0];
+  return 0;
+}
+extern "C" int insb200_maxabs(insb200_ctx *c, const void *u, double *m) {
+  API_PROLOG(c);
+  if (!u || !m) INS_FAIL(c, "NULL argument");
+  double o[4];
+  INS_TRY(DISPATCH(c, op_reduce, c, u, o));
+  *m = std::max(o[1], std::max(o[2], o[3]));
+  return 0;
+}
+
+namespace insb200 {
+// fused momentum + stage combination; variant 0 = one thread per cell, 1 = tiled (tiled.cuh)
+template <typename T, int D>
+static int launch_stage(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, bool smag) {
+  if (c->variant >= 1 && tiled_stage_supported<T, D>(c, g)) return launch_stage_tiled<T, D>(c, a, g, visc, rh, smag);
+  dim3 grd = cell_grid(c->nloc), blk = cell_block();
+  if (smag) k_momentum_stage<T, D, true><<<grd, blk, 0, c->stream>>>(a, g, visc, rh);
+  else k_momentum_stage<T, D, false><<<grd, blk, 0, c->stream>>>(a, g, visc, rh);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+}  // namespace insb200
+
+// =================================================================================================
+// time stepping (compact layout)
+// =================================================================================================
+namespace insb200 {
+
+struct Tableau {
+  int s;
+  const double *A;  // shifted, row-major s*s
+  const double *c;
+  bool need[INSB200_MAX_STAGES];  // k_j is read by a later stage
+};
+
+static int make_tableau(insb200_ctx *c, int s, const double *A, const double *cc, Tableau &tb) {
+  if (s < 1 || s > INSB200_MAX_STAGES) INS_FAIL(c, "number of stages out of range");
+  if (!A || !cc) INS_FAIL(c, "tableau is NULL");
+  tb.s = s; tb.A = A; tb.c = cc;
+  for (int j = 0; j < s; j++) {
+    tb.need[j] = false;
+    for (int l = j + 1; l < s; l++) if (A[l * s + j] != 0.0) tb.need[j] = true;
+    for (int l = 0; l < j; l++) if (A[l * s + j] != 0.0) INS_FAIL(c, "tableau is not explicit (shifted A must be lower triangular)");
+  }
+  return 0;
+}
+
+static int ensure_rk(insb200_ctx *c, const Tableau &tb, bool smag) {
+  INS_TRY(ensure_fft(c));
+  for (int b = 0; b < 3; b++) INS_TRY(ensure_vec(c, &c->ubuf[b]));
+  for (int j = 0; j < tb.s; j++) if (tb.need[j]) INS_TRY(ensure_vec(c, &c->kbuf[j]));
+  if (smag) INS_TRY(ensure_sigma(c));
+  return 0;
+}
+
+// one timestep!: state in ubuf[0] (compact), result in ubuf[0] (buffers rotated).
+template <typename T, int D>
+static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
+  const bool smag = !std::isnan(theta);
+  const Geo g = geo_compact(c);
+  const T visc = T(1) / T(c->Re);
+  const Rh<T> rh = make_rh<T>(c);
+  int cur = 0;
+  for (int i = 0; i < tb.s; i++) {
+    const int nxt = (cur == 1) ? 2 : 1;
+    // apply_bc_u! before momentum (step_explicit_runge_kutta.jl:19): wrap by index, halos over NCCL
+    INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, true, true)));
+    if (smag) INS_TRY((compute_sigma<T, D>(c, view_compact_c<T>(c, c->ubuf[cur]), g, theta)));
+    StageArgs<T> a;
+    memset(&a, 0, sizeof a);
+    const i64 goff = (i64)c->G * c->cplane;
+    a.u = (const T *)c->ubuf[cur] + goff;
+    a.u0 = (const T *)c->ubuf[0] + goff;
+    a.nk = 0;
+    for (int j = 0; j < i; j++) {
+      if (tb.A[i * tb.s + j] == 0.0) continue;  // exact: adds +-0
+      a.kin[a.nk] = (const T *)c->kbuf[j] + goff;
+      a.coef[a.nk] = T(dt) * T(tb.A[i * tb.s + j]);  // `dt * A[i,j]` formed first (:37)
+      a.nk++;
+    }
+    a.coef_self = T(dt) * T(tb.A[i * tb.s + i]);
+    a.kout = tb.need[i] ? (T *)c->kbuf[i] + goff : nullptr;
+    a.unew = (T *)c->ubuf[nxt] + goff;
+    a.force = c->force ? (const T *)c->force + goff : nullptr;
+    a.sigma = smag ? (const T *)c->sigma + goff : nullptr;
+    a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp; a.ssc = c->ccomp;
+    {
+      ScopedTimer tm(c, TM_STAGE);
+      INS_TRY((launch_stage<T, D>(c, a, g, visc, rh, smag)));
+    }
+    // apply_bc_u! + project! (:48-49): only the minus-side halo of u' is consumed by the divergence
+    INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, true, false)));
+    INS_TRY((project_view<T, D>(c, view_compact<T>(c, c->ubuf[nxt]), g)));
+    cur = nxt;
+  }
+  std::swap(c->ubuf[0], c->ubuf[cur]);
+  return 0;
+}
+
+template <typename T, int D>
+static int reduce_compact(insb200_ctx *c, double *out4) {
+  INS_TRY((halo_compact<T>(c, c->ubuf[0], D, true, false)));
+  return reduce_view<T, D>(c, view_compact_c<T>(c, c->ubuf[0]), geo_compact(c), out4);
+}
+
+template <typename T, int D>
+static int export_state(insb200_ctx *c, void *u) {
+  INS_TRY((export_field<T, D>(c, u, c->ubuf[0], D)));
+  return bc_fill<T, D>(c, u, D);  // final apply_bc_u! (:55): all ghosts valid on return
+}
+
+template <typename T, int D>
+static int op_rk_steps(insb200_ctx *c, void *u, double *t, double dt, int nsteps, const Tableau &tb, double theta,
+                       double *ke_hist, void *p_out) {
+  const bool smag = !std::isnan(theta);
+  INS_TRY(ensure_rk(c, tb, smag));
+  INS_TRY((import_field<T, D>(c, c->ubuf[0], u, D)));
+  double o[4];
+  if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[0] = o[0]; }
+  T tt = T(*t);
+  for (int n = 0; n < nsteps; n++) {
+    INS_TRY((rk_step_compact<T, D>(c, tb, dt, theta)));
+    tt = tt + T(tb.c[tb.s - 1]) * T(dt);  // t = tstart + c[i]*dt (:32)
+    if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[n + 1] = o[0]; }
+  }
+  *t = (double)tt;
+  INS_TRY((export_state<T, D>(c, u)));
+  if (p_out) INS_TRY((export_p<T, D>(c, p_out)));
+  return 0;
+}
+
+template <typename T, int D>
+static int op_solve_host(insb200_ctx *c, void *u_host, double t0, double tend, double dt, double cfl, int n_adapt,
+                         int max_steps, const Tableau &tb, double theta, double *ke_hist, int ke_cap, int *nsteps_out,
+                         double *t_out) {
+  const bool smag = !std::isnan(theta);
+  INS_TRY(ensure_rk(c, tb, smag));
+  const size_t bytes = (size_t)ghosted_elems(c) * D * sizeof(T);
+  INS_TRY(dev_alloc(c, &c->hostio, bytes));
+  INS_CUDA(c, cudaMemcpyAsync(c->hostio, u_host, bytes, cudaMemcpyHostToDevice, c->stream));
+  INS_TRY((import_field<T, D>(c, c->ubuf[0], c->hostio, D)));
+  double o[4];
+  int nk = 0;
+  if (ke_hist && nk < ke_cap) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[nk++] = o[0]; }
+  T t = T(t0);
+  const T te = T(tend);
+  int n = 0;
+  if (dt > 0) {
+    // fixed step (solver.jl:71-79): nstep = round((tend-tstart)/dt); dt = (tend-tstart)/nstep
+    long long nstep = llround((double)((te - t) / T(dt)));
+    if (nstep < 1) nstep = 1;
+    const T d = (te - t) / T((double)nstep);
+    if (max_steps > 0 && nstep > max_steps) nstep = max_steps;
+    for (; n < nstep; n++) {
+      INS_TRY((rk_step_compact<T, D>(c, tb, (double)d, theta)));
+      t = t + T(tb.c[tb.s - 1]) * d;
+      if (ke_hist && nk < ke_cap) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[nk++] = o[0]; }
+    }
+  } else {
+    // adaptive (solver.jl:53-69)
+    if (n_adapt < 1) n_adapt = 1;
+    T d = T(0);
+    while (t < te) {
+      if (n % n_adapt == 0) {
+        INS_TRY((reduce_compact<T, D>(c, o)));
+        d = T(cfl) * T(cfl_from_max<T>(c, o));
+      }
+      d = std::min(d, te - t);
+      INS_TRY((rk_step_compact<T, D>(c, tb, (double)d, theta)));
+      t = t + T(tb.c[tb.s - 1]) * d;
+      n++;
+      if (ke_hist && nk < ke_cap) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[nk++] = o[0]; }
+      if (max_steps > 0 && n >= max_steps) break;
+    }
+  }
+  INS_TRY((export_state<T, D>(c, c->hostio)));
+  INS_CUDA(c, cudaMemcpyAsync(u_host, c->hostio, bytes, cudaMemcpyDeviceToHost, c->stream));
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  if (nsteps_out) *nsteps_out = n;
+  if (t_out) *t_out = (double)t;
+  return 0;
+}
+
+}  // namespace insb200
+
+extern "C" int insb200_rk_step(insb200_ctx *c, void *u, double t, double dt, int s, const double *A, const double *cc,
+                               double theta, void *p_out) {
+  API_PROLOG(c);
+  if (!u) INS_FAIL(c, "u is NULL");
+  Tableau tb;
+  INS_TRY(make_tableau(c, s, A, cc, tb));
+  double tt = t;
+  return DISPATCH(c, op_rk_steps, c, u, &tt, dt, 1, tb, theta, nullptr, p_out);
+}
+
+extern "C" int insb200_rk_steps(insb200_ctx *c, void *u, double *t, double dt, int nsteps, int s, const double *A,
+                                const double *cc, double theta, double *ke_hist) {
+  API_PROLOG(c);
+  if (!u || !t) INS_FAIL(c, "NULL argument");
+  if (nsteps < 0) INS_FAIL(c, "nsteps < 0");
+  Tableau tb;
+  INS_TRY(make_tableau(c, s, A, cc, tb));
+  return DISPATCH(c, op_rk_steps, c, u, t, dt, nsteps, tb, theta, ke_hist, nullptr);
+}
+
+extern "C" int insb200_solve_unsteady_host(insb200_ctx *c, void *u_host, double t0, double tend, double dt, double cfl,
+                                           int n_adapt_dt, int max_steps, int s, const double *A, const double *cc,
+                                           double theta, double *ke_hist, int ke_cap, int *nsteps_out, double *t_out) {
+  API_PROLOG(c);
+  if (!u_host) INS_FAIL(c, "u_host is NULL");
+  if (!(tend >= t0)) INS_FAIL(c, "tend < t0");
+  Tableau tb;
+  INS_TRY(make_tableau(c, s, A, cc, tb));
+  return DISPATCH(c, op_solve_host, c, u_host, t0, tend, dt, cfl, n_adapt_dt, max_steps, tb, theta, ke_hist, ke_cap,
+                  nsteps_out, t_out);
+}
+
+// =================================================================================================
+// introspection
+// =================================================================================================
+extern "C" double insb200_model_bytes_per_cell_step(const insb200_ctx *c, int nstages) {
+  if (!c) return 0;
+  // RK44 = 3*4D + 6D + 4*[(D+1) + 4D + (2D+1)] = 46D + 8 words; generalised per stage:
+  // stages with one tableau entry 4D, final stage (3 + (s-1)) D; + D per stage with a stored force.
+  const int D = c->D, s = nstages;
+  double words = (s - 1) * 4.0 * D + (3.0 + (s - 1)) * D + s * ((D + 1) + 4.0 * D + (2.0 * D + 1));
+  if (c->force) words += (double)s * D;
+  return words * (double)esize(c);
+}
+extern "C" long long insb200_launch_count(const insb200_ctx *c) { return c ? c->launches : 0; }
+extern "C" long long insb200_fft_exec_count(const insb200_ctx *c) { return c ? c->fft_execs : 0; }
+extern "C" long long insb200_workspace_bytes(const insb200_ctx *c) { return c ? c->ws_bytes : 0; }
+
+static int drain_timers(insb200_ctx *c) {
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  for (auto &r : c->recs) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) { c->tm_ms[r.id] += ms; c->tm_cnt[r.id]++; }
+    c->pool.push_back(r.a);
+    c->pool.push_back(r.b);
+  }
+  c->recs.clear();
+  return 0;
+}
+extern "C" int insb200_set_profiling(insb200_ctx *c, int enable) {
+  API_PROLOG(c);
+  INS_TRY(drain_timers(c));
+  c->profiling = enable != 0;
+  return 0;
+}
+extern "C" int insb200_reset_timers(insb200_ctx *c) {
+  API_PROLOG(c);
+  INS_TRY(drain_timers(c));
+  for (int i = 0; i < TM_COUNT; i++) { c->tm_ms[i] = 0; c->tm_cnt[i] = 0; }
+  return 0;
+}
+extern "C" int insb200_timers(insb200_ctx *c, const char **names, double *ms, long long *counts, int cap, int *n) {
+  API_PROLOG(c);
+  INS_TRY(drain_timers(c));
+  int k = 0;
+  for (int i = 0; i < TM_COUNT && k < cap; i++) {
+    if (!c->tm_cnt[i]) continue;
+    names[k] = kTimerNames[i]; ms[k] = c->tm_ms[i]; counts[k] = c->tm_cnt[i];
+    k++;
+  }
+  if (n) *n = k;
+  return 0;
+}
+extern "C" int insb200_set_variant(insb200_ctx *c, int variant) {
+  if (!c) return 1;
+  c->variant = variant;
+  return 0;
+}

@@ -1,0 +1,453 @@
+// stencil.cuh -- device arithmetic of the staggered-grid operators and the "one thread per cell"
+// kernels that work on ANY layout (reference/ghosted or compact) through a View + Geo pair.
+//
+// Arithmetic contract (checked bit-for-bit against the oracle when h is a power of two):
+//   * same operation order as the reference kernels (cited per function),
+//   * the library is compiled with -fmad=false, so a*b+c is never contracted (Julia does not
+//     contract either),
+//   * x / h is evaluated as x * (1/h): exact when h is a power of two (every BASELINE config:
+//     unit box, n = 2^m), otherwise within 1 ulp per division;  x/2, x/4 -> x*0.5, x*0.25 (exact).
+#pragma once
+#include "ctx.cuh"
+
+namespace insb200 {
+
+// ---------------------------------------------------------------------------------------------
+// neighbour addressing
+// ---------------------------------------------------------------------------------------------
+template <int D, int R>
+struct Sten {
+  i64 ox[2 * R + 1], oy[2 * R + 1], oz[2 * R + 1];
+  __device__ __forceinline__ Sten(const Geo &g, i64 sy, i64 sz, int i, int j, int k) {
+#pragma unroll
+    for (int d = -R; d <= R; d++) {
+      int ii = i + d, jj = j + d, kk = k + d;
+      if (g.wrap[0]) { if (ii < 0) ii += g.n[0]; else if (ii >= g.n[0]) ii -= g.n[0]; }
+      if (g.wrap[1]) { if (jj < 0) jj += g.n[1]; else if (jj >= g.n[1]) jj -= g.n[1]; }
+      ox[d + R] = ii;
+      oy[d + R] = (i64)jj * sy;
+      if (D == 3) {
+        if (g.wrap[2]) { if (kk < 0) kk += g.n[2]; else if (kk >= g.n[2]) kk -= g.n[2]; }
+        oz[d + R] = (i64)kk * sz;
+      } else {
+        oz[d + R] = 0;
+      }
+    }
+  }
+  __device__ __forceinline__ i64 at(int dx, int dy, int dz) const {
+    return ox[dx + R] + oy[dy + R] + (D == 3 ? oz[dz + R] : 0);
+  }
+};
+
+template <typename T, int D, int R>
+struct Acc {  // read accessor of a multi-component field at a stencil
+  const T *__restrict__ p;
+  i64 sc;
+  const Sten<D, R> &s;
+  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
+    return __ldg(p + c * sc + s.at(dx, dy, dz));
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// convection_diffusion_kernel!  src/operators.jl:647-690 (also convection_kernel! :392-415 and
+// diffusion_kernel! :551-573 through the CONV / DIFF switches), one component `a` at one cell.
+// `U(c,dx,dy,dz)` returns u[I + (dx,dy,dz), c].
+// ---------------------------------------------------------------------------------------------
+template <typename T, int D, bool CONV, bool DIFF, class A>
+__device__ __forceinline__ T convdiff_comp(const A &U, const int a, const T visc, const T (&rh)[3]) {
+  const T half = T(0.5);
+  T f = T(0);
+  const T uI = U(a, 0, 0, 0);
+  const int ax = (a == 0), ay = (a == 1), az = (a == 2);
+#pragma unroll
+  for (int b = 0; b < D; b++) {
+    const int bx = (b == 0), by = (b == 1), bz = (b == 2);
+    const T um = U(a, -bx, -by, -bz);
+    const T up = U(a, bx, by, bz);
+    T uu1 = T(0), uu2 = T(0), d1 = T(0), d2 = T(0);
+    if (CONV) {
+      const T ua1 = (um + uI) * half;
+      const T ua2 = (uI + up) * half;
+      const T ub1 = half * U(b, -bx, -by, -bz) + half * U(b, ax - bx, ay - by, az - bz);
+      const T ub2 = half * U(b, 0, 0, 0) + half * U(b, ax, ay, az);
+      uu1 = ua1 * ub1;
+      uu2 = ua2 * ub2;
+    }
+    if (DIFF) {
+      d1 = (uI - um) * rh[b];
+      d2 = (up - uI) * rh[b];
+    }
+    if (CONV && DIFF) f += (visc * (d2 - d1) - (uu2 - uu1)) * rh[b];
+    else if (CONV) f -= (uu2 - uu1) * rh[b];
+    else f += visc * (d2 - d1) * rh[b];
+  }
+  return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Smagorinsky: dx / grad / smagtensor!  src/operators.jl:1023-1033, 1072-1088, 1135-1151.
+// sigma is symmetric; stored components (index): 2-D: xx(0) xy(1) yy(2); 3-D: xx(0) xy(1) xz(2)
+// yy(3) yz(4) zz(5).
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ int symidx(int D, int a, int b) {
+  if (a > b) { int t = a; a = b; b = t; }
+  return D == 2 ? a + b : (a == 0 ? b : (a == 1 ? 2 + b : 5));
+}
+
+template <typename T, int D, class A>
+__device__ __forceinline__ T ddx(const A &U, const int a, const int b, const T (&rh)[3]) {
+  const int ax = (a == 0), ay = (a == 1), az = (a == 2);
+  const int bx = (b == 0), by = (b == 1), bz = (b == 2);
+  if (a == b) return (U(a, 0, 0, 0) - U(a, -bx, -by, -bz)) * rh[b];
+  return ((U(a, bx, by, bz) - U(a, 0, 0, 0)) * rh[b] +
+          (U(a, bx - ax, by - ay, bz - az) - U(a, -ax, -ay, -az)) * rh[b] +
+          (U(a, 0, 0, 0) - U(a, -bx, -by, -bz)) * rh[b] +
+          (U(a, -ax, -ay, -az) - U(a, -ax - bx, -ay - by, -az - bz)) * rh[b]) * T(0.25);
+}
+
+// sig[symidx] at one p-cell; c_eddy = theta^2 * d^2 (formed on the host in T, left to right)
+template <typename T, int D, class A>
+__device__ __forceinline__ void smag_sigma(const A &U, const T c_eddy, const T (&rh)[3], T (&sig)[6]) {
+  T G[3][3];
+#pragma unroll
+  for (int a = 0; a < D; a++)
+#pragma unroll
+    for (int b = 0; b < D; b++) G[a][b] = ddx<T, D>(U, a, b, rh);
+  T S[3][3];
+#pragma unroll
+  for (int a = 0; a < D; a++)
+#pragma unroll
+    for (int b = 0; b < D; b++) S[a][b] = (G[a][b] + G[b][a]) * T(0.5);
+  // sum(S .* S): column-major order of the SMatrix (row index fastest), left fold
+  T ss = T(0);
+  bool first = true;
+#pragma unroll
+  for (int b = 0; b < D; b++)
+#pragma unroll
+    for (int a = 0; a < D; a++) {
+      const T t = S[a][b] * S[a][b];
+      ss = first ? t : ss + t;
+      first = false;
+    }
+  const T eddy = c_eddy * sqrt(T(2) * ss);
+  const T two_eddy = T(2) * eddy;
+#pragma unroll
+  for (int a = 0; a < D; a++)
+#pragma unroll
+    for (int b = a; b < D; b++) sig[symidx(D, a, b)] = two_eddy * S[a][b];
+}
+
+// divoftensor_kernel!  src/operators.jl:1205-1238, one component at one u-point.
+// `Sg(idx,dx,dy,dz)` returns sigma[I + (dx,dy,dz)][component idx].
+template <typename T, int D, class A>
+__device__ __forceinline__ T divsigma_comp(const A &Sg, const int a, const T (&rh)[3]) {
+  const int ax = (a == 0), ay = (a == 1), az = (a == 2);
+  T s = T(0);
+#pragma unroll
+  for (int b = 0; b < D; b++) {
+    const int bx = (b == 0), by = (b == 1), bz = (b == 2);
+    const int c = symidx(D, a, b);
+    T s1, s2;
+    if (a == b) {
+      s2 = Sg(c, bx, by, bz);
+      s1 = Sg(c, 0, 0, 0);
+    } else {
+      s2 = (Sg(c, 0, 0, 0) + Sg(c, bx, by, bz) + Sg(c, ax + bx, ay + by, az + bz) + Sg(c, ax, ay, az)) * T(0.25);
+      s1 = (Sg(c, -bx, -by, -bz) + Sg(c, 0, 0, 0) + Sg(c, ax - bx, ay - by, az - bz) + Sg(c, ax, ay, az)) * T(0.25);
+    }
+    s += (s2 - s1) * rh[b];
+  }
+  return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernels: one thread per cell, x fastest -> coalesced; neighbours through L1/L2
+// ---------------------------------------------------------------------------------------------
+#define INS_CELL_IDX(g)                                           \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;            \
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;            \
+  const int k = blockIdx.z;                                       \
+  if (i >= (g).n[0] || j >= (g).n[1]) return;
+
+template <typename T>
+struct Rh {
+  T v[3];
+};
+
+// copy the interior of one view into another (import / export between layouts); nc components
+template <typename T>
+__global__ void k_copy_view(View<T> dst, View<const T> src, Geo g, int nc) {
+  INS_CELL_IDX(g)
+  for (int c = 0; c < nc; c++)
+    dst.p[c * dst.sc + k * dst.sz + j * dst.sy + i] = src.p[c * src.sc + k * src.sz + j * src.sy + i];
+}
+
+// periodic ghost fill of a reference-layout array: the two ghost layers normal to `axis`, over
+// the FULL extent of the other axes; the source index is wrapped in every axis, which equals the
+// reference's axis-by-axis slab copies (src/boundary_conditions.jl:276-288, 306-318).
+// base = pointer to element (1,1,1) Julia of component 0; N = n + 2.  If `only_local` the axis
+// given by skip_axis is not wrapped (its ghosts come from the neighbour ranks).
+template <typename T>
+__global__ void k_bc_axis(T *base, i64 sy, i64 sz, i64 sc, int n0, int n1, int n2, int D, int nc, int axis,
+                          int skip_axis) {
+  // thread space: the other two axes cover -1..n (N points), the `axis` dimension has 2 layers
+  int t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  int t1 = blockIdx.y * blockDim.y + threadIdx.y;
+  int side = blockIdx.z & 1;
+  int c = blockIdx.z >> 1;
+  int n[3] = {n0, n1, n2};
+  int idx[3];
+  int o0 = axis == 0 ? 1 : 0, o1 = axis == 2 ? 1 : 2;  // the two non-axis dims
+  if (D == 2) { o0 = axis == 0 ? 1 : 0; o1 = 2; }
+  if (t0 >= n[o0] + 2) return;
+  if (D == 3 ? (t1 >= n[o1] + 2) : (t1 >= 1)) return;
+  idx[o0] = t0 - 1;
+  idx[o1] = D == 3 ? t1 - 1 : 0;
+  idx[axis] = side ? n[axis] : -1;
+  if (D == 2) idx[2] = 0;
+  int s[3];
+  for (int d = 0; d < 3; d++) {
+    s[d] = idx[d];
+    if (d < D && d != skip_axis) { if (s[d] < 0) s[d] += n[d]; else if (s[d] >= n[d]) s[d] -= n[d]; }
+  }
+  T *pc = base + c * sc;
+  pc[idx[2] * sz + idx[1] * sy + idx[0]] = pc[s[2] * sz + s[1] * sy + s[0]];
+}
+
+// momentum! (src/operators.jl:967-976) = convectiondiffusion! + applybodyforce! written (not
+// accumulated) into F's interior.  force may be null.
+template <typename T, int D, bool CONV, bool DIFF>
+__global__ void k_momentum(View<T> F, View<const T> u, View<const T> force, Geo g, T visc, Rh<T> rh) {
+  INS_CELL_IDX(g)
+  Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
+  Acc<T, D, 1> U{u.p, u.sc, s};
+  const i64 o = k * F.sz + j * F.sy + i;
+#pragma unroll
+  for (int a = 0; a < D; a++) {
+    T f = convdiff_comp<T, D, CONV, DIFF>(U, a, visc, rh.v);
+    if (force.p) f = f + force.p[a * force.sc + k * force.sz + j * force.sy + i];
+    F.p[a * F.sc + o] = f;
+  }
+}
+
+// Fused momentum + RK stage combination (step_explicit_runge_kutta.jl:21-38), compact layout.
+//   k_i  = convdiff(u) [+ force] [+ div sigma]                 -> kout (if non-null)
+//   unew = u0 + sum_j coef[j]*kin[j] (ascending j) + coef_self*k_i
+template <typename T>
+struct StageArgs {
+  const T *u;       // stage input (ghost planes valid when not wrapped)
+  const T *u0;      // ustart
+  const T *kin[INSB200_MAX_STAGES];
+  T coef[INSB200_MAX_STAGES];
+  int nk;
+  T coef_self;
+  T *kout;          // nullable
+  T *unew;
+  const T *force;   // nullable (compact)
+  const T *sigma;   // nullable (compact, ghost planes valid when not wrapped)
+  i64 sy, sz, sc;   // strides shared by all compact vector buffers
+  i64 ssc;          // component stride of sigma
+};
+
+template <typename T, int D, bool SMAG>
+__global__ void k_momentum_stage(StageArgs<T> A, Geo g, T visc, Rh<T> rh) {
+  INS_CELL_IDX(g)
+  Sten<D, 1> s(g, A.sy, A.sz, i, j, k);
+  Acc<T, D, 1> U{A.u, A.sc, s};
+  Acc<T, D, 1> Sg{A.sigma, A.ssc, s};
+  const i64 o = k * A.sz + j * A.sy + i;
+#pragma unroll
+  for (int a = 0; a < D; a++) {
+    T f = convdiff_comp<T, D, true, true>(U, a, visc, rh.v);
+    if (A.force) f = f + A.force[a * A.sc + o];
+    if (SMAG) f = f + divsigma_comp<T, D>(Sg, a, rh.v);
+    if (A.kout) A.kout[a * A.sc + o] = f;
+    T acc = A.u0[a * A.sc + o];
+    for (int q = 0; q < A.nk; q++) acc = acc + A.coef[q] * A.kin[q][a * A.sc + o];
+    acc = acc + A.coef_self * f;
+    A.unew[a * A.sc + o] = acc;
+  }
+}
+
+// smagtensor! on all local p-cells (src/operators.jl:1135-1151) into the compact sigma buffer
+template <typename T, int D>
+__global__ void k_smagtensor(View<T> sg, View<const T> u, Geo g, T c_eddy, Rh<T> rh) {
+  INS_CELL_IDX(g)
+  Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
+  Acc<T, D, 1> U{u.p, u.sc, s};
+  T sig[6];
+  smag_sigma<T, D>(U, c_eddy, rh.v, sig);
+  const i64 o = k * sg.sz + j * sg.sy + i;
+#pragma unroll
+  for (int c = 0; c < D * (D + 1) / 2; c++) sg.p[c * sg.sc + o] = sig[c];
+}
+
+// divoftensor! (src/operators.jl:1166-1238): sigma view geometry gs (compact), output any layout
+template <typename T, int D>
+__global__ void k_divtensor(View<T> out, View<const T> sg, Geo gs, Rh<T> rh) {
+  INS_CELL_IDX(gs)
+  Sten<D, 1> s(gs, sg.sy, sg.sz, i, j, k);
+  Acc<T, D, 1> Sg{sg.p, sg.sc, s};
+  const i64 o = k * out.sz + j * out.sy + i;
+#pragma unroll
+  for (int a = 0; a < D; a++) out.p[a * out.sc + o] = divsigma_comp<T, D>(Sg, a, rh.v);
+}
+
+// divergence! (+ scalewithvolume!)  src/operators.jl:106-125, 81-95:  out = (sum_a (u-um)/h_a) * vol
+template <typename T, int D>
+__global__ void k_divergence(View<T> out, View<const T> u, Geo g, Rh<T> rh, T vol, int scale) {
+  INS_CELL_IDX(g)
+  Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
+  Acc<T, D, 1> U{u.p, u.sc, s};
+  T d = T(0);
+#pragma unroll
+  for (int a = 0; a < D; a++) d += (U(a, 0, 0, 0) - U(a, -(a == 0), -(a == 1), -(a == 2))) * rh.v[a];
+  if (scale) d = d * vol;
+  out.p[k * out.sz + j * out.sy + i] = d;
+}
+
+// pressuregradient! / applypressure!  src/operators.jl:159-178, 214-233.
+// MODE 0: G = grad p ; MODE 1: u -= grad p.  gp = geometry (wrap flags) of the p view.
+template <typename T, int D, int MODE>
+__global__ void k_gradient(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
+  INS_CELL_IDX(gp)
+  Sten<D, 1> s(gp, p.sy, p.sz, i, j, k);
+  const T p0 = __ldg(p.p + s.at(0, 0, 0));
+  const i64 o = k * out.sz + j * out.sy + i;
+#pragma unroll
+  for (int a = 0; a < D; a++) {
+    const T gr = (__ldg(p.p + s.at(a == 0, a == 1, a == 2)) - p0) * rh.v[a];
+    if (MODE == 0) out.p[a * out.sc + o] = gr;
+    else out.p[a * out.sc + o] = out.p[a * out.sc + o] - gr;
+  }
+}
+
+// whole-array scale (scalewithvolume! on the reference layout, ghosts included)
+template <typename T>
+__global__ void k_scale(T *p, i64 n, T f) {
+  i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) p[t] = p[t] * f;
+}
+
+// spectral Poisson: phat = -phat / ((ax+ay)+az) * invN ; zero mode -> 0  (src/pressure.jl:326-341;
+// the 1/N of ldiv! :344 is folded in here).  Layout (kx fastest, ky, kz); kx0/ky0 = global offsets.
+template <typename T, typename C, int D>
+__global__ void k_poisson_scale(C *phat, const T *__restrict__ ax, const T *__restrict__ ay,
+                                const T *__restrict__ az, int nkx, int nky, int nkz, int kx0, T invN) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z;
+  if (i >= nkx || j >= nky) return;
+  T den = ax[kx0 + i] + ay[j];
+  if (D == 3) den = den + az[k];
+  const i64 o = ((i64)k * nky + j) * nkx + i;
+  C v = phat[o];
+  if (kx0 + i == 0 && j == 0 && k == 0) {
+    v.x = T(0);
+    v.y = T(0);
+  } else {
+    v.x = (-v.x / den) * invN;
+    v.y = (-v.y / den) * invN;
+  }
+  phat[o] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// reductions: per-block partials with warp shuffles, finished by a second tiny kernel
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_max(double v) {
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// partial[block] = sum over the block's cells of  (sum_a u[I,a]^2 + u[I-e_a,a]^2)/4 * vol
+// (kinetic_energy! elast! src/operators.jl:1531-1539 + scalewithvolume! + sum); per-cell value in
+// T as the reference, accumulation in double.  Also per-component max |u| (get_cfl_timestep!
+// src/solver.jl:110-122: min_I h/|u| == h / max_I |u| because fl(h/x) is monotone).
+template <typename T, int D>
+__global__ void k_reduce_partials(View<const T> u, Geo g, T vol, double *part_ke, double *part_max) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z;
+  double ke = 0.0;
+  double mx[3] = {0.0, 0.0, 0.0};
+  if (i < g.n[0] && j < g.n[1]) {
+    Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
+    Acc<T, D, 1> U{u.p, u.sc, s};
+    T kk = T(0);
+#pragma unroll
+    for (int a = 0; a < D; a++) {
+      const T v = U(a, 0, 0, 0), vm = U(a, -(a == 0), -(a == 1), -(a == 2));
+      kk += v * v + vm * vm;
+      mx[a] = fabs((double)v);
+    }
+    kk = kk * T(0.25);
+    ke = (double)(kk * vol);
+  }
+  __shared__ double sh[4][32];
+  const int tid = threadIdx.y * blockDim.x + threadIdx.x;
+  const int lane = tid & 31, w = tid >> 5, nw = (blockDim.x * blockDim.y + 31) >> 5;
+  ke = warp_sum(ke);
+#pragma unroll
+  for (int a = 0; a < 3; a++) mx[a] = warp_max(mx[a]);
+  if (lane == 0) { sh[0][w] = ke; sh[1][w] = mx[0]; sh[2][w] = mx[1]; sh[3][w] = mx[2]; }
+  __syncthreads();
+  if (w == 0) {
+    ke = lane < nw ? sh[0][lane] : 0.0;
+    double m0 = lane < nw ? sh[1][lane] : 0.0, m1 = lane < nw ? sh[2][lane] : 0.0, m2 = lane < nw ? sh[3][lane] : 0.0;
+    ke = warp_sum(ke); m0 = warp_max(m0); m1 = warp_max(m1); m2 = warp_max(m2);
+    if (lane == 0) {
+      const i64 b = ((i64)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+      part_ke[b] = ke;
+      part_max[3 * b + 0] = m0; part_max[3 * b + 1] = m1; part_max[3 * b + 2] = m2;
+    }
+  }
+}
+
+// out[0] = sum part_ke ; out[1..3] = max part_max   (single block, fixed order -> deterministic)
+__global__ void k_reduce_final(const double *part_ke, const double *part_max, i64 nb, double *out) {
+  double ke = 0.0, m0 = 0.0, m1 = 0.0, m2 = 0.0;
+  for (i64 b = threadIdx.x; b < nb; b += blockDim.x) {
+    ke += part_ke[b];
+    m0 = fmax(m0, part_max[3 * b]); m1 = fmax(m1, part_max[3 * b + 1]); m2 = fmax(m2, part_max[3 * b + 2]);
+  }
+  __shared__ double sh[4][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  ke = warp_sum(ke); m0 = warp_max(m0); m1 = warp_max(m1); m2 = warp_max(m2);
+  if (lane == 0) { sh[0][w] = ke; sh[1][w] = m0; sh[2][w] = m1; sh[3][w] = m2; }
+  __syncthreads();
+  if (w == 0) {
+    ke = lane < nw ? sh[0][lane] : 0.0; m0 = lane < nw ? sh[1][lane] : 0.0;
+    m1 = lane < nw ? sh[2][lane] : 0.0; m2 = lane < nw ? sh[3][lane] : 0.0;
+    ke = warp_sum(ke); m0 = warp_max(m0); m1 = warp_max(m1); m2 = warp_max(m2);
+    if (lane == 0) { out[0] = ke; out[1] = m0; out[2] = m1; out[3] = m2; }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// distributed-FFT pack / unpack (nranks > 1).  Spectrum after the in-slab transform:
+//   S[zl][ky][kx], kx in [0,nxh) fastest.  Peer q owns kx in [q*kxc, min((q+1)*kxc, nxh)).
+// pack:   B[q][zl][ky][kxq]   = S[zl][ky][q*kxc + kxq]      (block stride = kxc*ny*nzl, dense inside)
+// after the all-to-all rank r holds R[q][zl_q][ky][kxl] = all z for its kx chunk: (kxl fastest, ky, z)
+// unpack is the inverse of pack on the way back.
+// ---------------------------------------------------------------------------------------------
+template <typename C>
+__global__ void k_fft_pack(C *B, const C *__restrict__ S, int nxh, i64 rows /* ny*nzl (or nyl in 2-D) */, int kxc,
+                           int dir /*0: S->B, 1: B->S*/) {
+  const int i = blockIdx.y * blockDim.x + threadIdx.x;                  // kx
+  const i64 r = (i64)blockIdx.x * blockDim.y + threadIdx.y;              // row
+  if (i >= nxh || r >= rows) return;
+  const int q = i / kxc;
+  const int kq = i - q * kxc;
+  const int w = min(kxc, nxh - q * kxc);  // width of q's chunk
+  const i64 bo = (i64)q * kxc * rows + r * w + kq;
+  if (dir == 0) B[bo] = S[r * nxh + i];
+  else ((C *)S)[r * nxh + i] = B[bo];
+}
+
+}  // namespace insb200
