@@ -175,3 +175,478 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
         setup.issteadybodyforce = True
         ctx.call("insb200_set_bodyforce", _ptr(setup.bodyforce))
     return setup
+
+
+# --------------------------------------------------------------------------------------------
+# fields
+# --------------------------------------------------------------------------------------------
+def _ptr(t):
+    if t is None:
+        return None
+    if not (isinstance(t, torch.Tensor) and t.is_cuda and t.is_contiguous()):
+        raise TypeError("fields must be contiguous CUDA tensors (see to_device)")
+    return C.c_void_p(t.data_ptr())
+
+
+def _check(t, setup, vector):
+    g = setup.grid
+    shape = tuple(reversed(g.N)) if not vector else (g.dimension,) + tuple(reversed(g.N))
+    if tuple(t.shape) != shape or t.dtype != setup.tdtype:
+        raise ValueError(f"field has shape {tuple(t.shape)} / {t.dtype}, expected {shape} / {setup.tdtype}")
+    return t
+
+
+def scalarfield(setup):
+    """src/initializers.jl:1-2"""
+    return torch.zeros(tuple(reversed(setup.grid.N)), dtype=setup.tdtype, device=setup.device)
+
+
+def vectorfield(setup):
+    """src/initializers.jl:4-6"""
+    g = setup.grid
+    return torch.zeros((g.dimension,) + tuple(reversed(g.N)), dtype=setup.tdtype, device=setup.device)
+
+
+def to_device(a, setup):
+    """Julia-shaped NumPy array `(N1,..,ND[,D])` -> device field (same memory image)."""
+    a = np.asfortranarray(np.asarray(a, dtype=setup.grid.T))
+    return torch.from_numpy(np.ascontiguousarray(a.T)).to(setup.device)
+
+
+def to_host(t):
+    """device field -> Julia-shaped NumPy array (Fortran order)."""
+    return t.detach().cpu().numpy().T
+
+
+def _sync_stream(setup):
+    # run the library on torch's current stream so that torch ops and kernels are ordered
+    s = torch.cuda.current_stream(setup.device).cuda_stream
+    setup.ctx.call("insb200_set_stream", C.c_void_p(s))
+
+
+# --------------------------------------------------------------------------------------------
+# operators (in-place `f_` = Julia `f!`, allocating twins without the underscore)
+# --------------------------------------------------------------------------------------------
+def apply_bc_u_(u, t, setup):
+    """apply_bc_u!(u, t, setup)  src/boundary_conditions.jl:159-167"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_apply_bc_u", _ptr(_check(u, setup, True)))
+    return u
+
+
+def apply_bc_p_(p, t, setup):
+    """apply_bc_p!(p, t, setup)  src/boundary_conditions.jl:197-206"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_apply_bc_p", _ptr(_check(p, setup, False)))
+    return p
+
+
+def apply_bc_u(u, t, setup):
+    return apply_bc_u_(u.clone(), t, setup)
+
+
+def apply_bc_p(p, t, setup):
+    return apply_bc_p_(p.clone(), t, setup)
+
+
+def momentum_(F, u, temp, t, setup):
+    """momentum!(F, u, temp, t, setup)  src/operators.jl:967-976"""
+    if temp is not None:
+        raise NotImplementedError("temperature is outside the B200 hot path")
+    _sync_stream(setup)
+    setup.ctx.call("insb200_momentum", _ptr(_check(F, setup, True)), _ptr(_check(u, setup, True)), float(t))
+    return F
+
+
+def momentum(u, temp, t, setup):
+    return momentum_(vectorfield(setup), u, temp, t, setup)
+
+
+def _convdiff(u, setup, terms):
+    F = vectorfield(setup)
+    _sync_stream(setup)
+    setup.ctx.call("insb200_convectiondiffusion", _ptr(F), _ptr(_check(u, setup, True)), terms)
+    return F
+
+
+def convection(u, setup):
+    """convection(u, setup)  src/operators.jl:366-415"""
+    return _convdiff(u, setup, 1)
+
+
+def diffusion(u, setup):
+    """diffusion(u, setup)  src/operators.jl:537-573"""
+    return _convdiff(u, setup, 2)
+
+
+def convectiondiffusion(u, setup):
+    """convectiondiffusion!(zero(u), u, setup)  src/operators.jl:634-690"""
+    return _convdiff(u, setup, 3)
+
+
+def divergence_(div, u, setup):
+    """divergence!(div, u, setup)  src/operators.jl:106-115"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_divergence", _ptr(_check(div, setup, False)), _ptr(_check(u, setup, True)))
+    return div
+
+
+def divergence(u, setup):
+    return divergence_(scalarfield(setup), u, setup)
+
+
+def scalewithvolume_(p, setup):
+    """scalewithvolume!(p, setup)  src/operators.jl:81-95"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_scalewithvolume", _ptr(_check(p, setup, False)))
+    return p
+
+
+def pressuregradient_(G, p, setup):
+    """pressuregradient!(G, p, setup)  src/operators.jl:159-168"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_pressuregradient", _ptr(_check(G, setup, True)), _ptr(_check(p, setup, False)))
+    return G
+
+
+def pressuregradient(p, setup):
+    return pressuregradient_(vectorfield(setup), p, setup)
+
+
+def applypressure_(u, p, setup):
+    """applypressure!(u, p, setup)  src/operators.jl:214-223"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_applypressure", _ptr(_check(u, setup, True)), _ptr(_check(p, setup, False)))
+    return u
+
+
+def applypressure(u, p, setup):
+    return applypressure_(u.clone(), p, setup)
+
+
+def psolver_spectral(setup):
+    """psolver_spectral(setup)  src/pressure.jl:289-351: returns `psolve!(p)` (in place)."""
+
+    def psolve_(p):
+        _sync_stream(setup)
+        setup.ctx.call("insb200_psolve_spectral", _ptr(_check(p, setup, False)))
+        return p
+
+    psolve_.setup = setup
+    return psolve_
+
+
+def default_psolver(setup):
+    """default_psolver(setup)  src/pressure.jl:85-98 (periodic + uniform -> spectral)."""
+    return psolver_spectral(setup)
+
+
+def poisson_(psolver, f):
+    """poisson!(psolver, f)  src/pressure.jl:22"""
+    return psolver(f)
+
+
+def poisson(psolver, f):
+    return psolver(f.clone())
+
+
+def project_(u, setup, psolver=None, p=None):
+    """project!(u, setup; psolver, p)  src/pressure.jl:69-82"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_project", _ptr(_check(u, setup, True)), _ptr(p) if p is not None else None)
+    return u
+
+
+def project(u, setup, psolver=None):
+    return project_(u.clone(), setup, psolver)
+
+
+def pressure_(p, u, temp, t, setup, psolver=None, F=None):
+    """pressure!(p, u, temp, t, setup; psolver, F)  src/pressure.jl:41-49"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_pressure", _ptr(_check(p, setup, False)), _ptr(_check(u, setup, True)), float(t))
+    return p
+
+
+def pressure(u, temp, t, setup, psolver=None):
+    return pressure_(scalarfield(setup), u, temp, t, setup, psolver)
+
+
+def smagorinsky_closure(setup):
+    """smagorinsky_closure(setup)  src/operators.jl:1294-1305: m(u, theta) -> s (same buffer
+    every call, like the reference)."""
+    s = vectorfield(setup)
+
+    def closure(u, theta):
+        _sync_stream(setup)
+        setup.ctx.call("insb200_smagorinsky", _ptr(s), _ptr(_check(u, setup, True)), float(theta))
+        return s
+
+    closure.is_smagorinsky = True
+    return closure
+
+
+def total_kinetic_energy(u, setup):
+    """total_kinetic_energy(u, setup)  src/operators.jl:1551-1556"""
+    _sync_stream(setup)
+    out = C.c_double()
+    setup.ctx.call("insb200_kinetic_energy", _ptr(_check(u, setup, True)), C.byref(out))
+    return out.value
+
+
+def get_cfl_timestep_(buf, u, setup):
+    """get_cfl_timestep!(buf, u, setup)  src/solver.jl:101-125 (`buf` is unused: one fused reduction)."""
+    _sync_stream(setup)
+    out = C.c_double()
+    setup.ctx.call("insb200_cfl_dt", _ptr(_check(u, setup, True)), C.byref(out))
+    return setup.grid.T(out.value)
+
+
+def maxabs(u, setup):
+    """maximum(abs, u)  src/processors.jl:67"""
+    _sync_stream(setup)
+    out = C.c_double()
+    setup.ctx.call("insb200_maxabs", _ptr(_check(u, setup, True)), C.byref(out))
+    return out.value
+
+
+# --------------------------------------------------------------------------------------------
+# time stepping  (src/time_steppers)
+# --------------------------------------------------------------------------------------------
+class ExplicitRungeKuttaMethod:
+    """ExplicitRungeKuttaMethod{T}  src/time_steppers/methods.jl:184-190 (A, c already shifted)."""
+
+    def __init__(self, A, b, c, r, p_add_solve=True):
+        self.A, self.b, self.c, self.r, self.p_add_solve = A, b, c, r, p_add_solve
+
+
+def runge_kutta_method(A, b, c, r, T=np.float64, **kw):
+    """runge_kutta_method  src/time_steppers/methods.jl:222-240: explicit tableaux are shifted,
+    A = [A[2:end,:]; b'], c = [c[2:end]; 1]."""
+    A = np.array(A, dtype=np.float64)
+    b = np.array(b, dtype=np.float64)
+    c = np.array(c, dtype=np.float64)
+    s = A.shape[0]
+    if not (A.shape == (s, s) and len(b) == s and len(c) == s):
+        raise ValueError("A, b, and c must have the same sizes")
+    if not np.allclose(np.triu(A), 0):
+        raise NotImplementedError("implicit Runge-Kutta methods are outside the B200 hot path")
+    A = np.vstack((A[1:, :], b[None, :])).astype(T)
+    c = np.concatenate((c[1:], [1.0])).astype(T)
+    return ExplicitRungeKuttaMethod(A, b.astype(T), c, T(r), **kw)
+
+
+class RKMethods:
+    """The explicit tableaux of src/time_steppers/RKMethods.jl that the examples use; any other
+    explicit tableau can be passed through `runge_kutta_method`."""
+
+    @staticmethod
+    def FE11(**kw):  # RKMethods.jl: forward Euler
+        return runge_kutta_method([[0]], [1], [0], 1, **kw)
+
+    @staticmethod
+    def SSP22(**kw):
+        return runge_kutta_method([[0, 0], [1, 0]], [1 / 2, 1 / 2], [0, 1], 1, **kw)
+
+    @staticmethod
+    def RK33P2(**kw):  # RKMethods.jl:505-511
+        return runge_kutta_method([[0, 0, 0], [1 / 3, 0, 0], [-1, 2, 0]], [0, 3 / 4, 1 / 4], [0, 1 / 3, 1], 0, **kw)
+
+    @staticmethod
+    def RK44(**kw):  # RKMethods.jl:515-521
+        A = [[0, 0, 0, 0], [1 / 2, 0, 0, 0], [0, 1 / 2, 0, 0], [0, 0, 1, 0]]
+        return runge_kutta_method(A, [1 / 6, 1 / 3, 1 / 3, 1 / 6], np.sum(np.array(A), axis=1), 0, **kw)
+
+    @staticmethod
+    def RK44C2(**kw):  # RKMethods.jl:524-530
+        A = [[0, 0, 0, 0], [1 / 4, 0, 0, 0], [0, 1 / 2, 0, 0], [1, -2, 2, 0]]
+        return runge_kutta_method(A, [1 / 6, 0, 2 / 3, 1 / 6], np.sum(np.array(A), axis=1), 0, **kw)
+
+
+def ode_method_cache(method, setup):
+    """ode_method_cache(method, setup)  time_stepper_caches.jl:34-49.  The stage buffers
+    (ustart, ku, p) are owned by the library context, so the cache is only a token."""
+    return SimpleNamespace(owner="libinsb200", nstage=len(method.b))
+
+
+def create_stepper(method, setup, psolver=None, u=None, temp=None, t=0.0, n=0):
+    """create_stepper(method; setup, psolver, u, temp, t, n=0)  step_explicit_runge_kutta.jl:1-2"""
+    if temp is not None:
+        raise NotImplementedError("temperature is outside the B200 hot path")
+    return SimpleNamespace(setup=setup, psolver=psolver, u=u, temp=None, t=setup.grid.T(t), n=n)
+
+
+def _tableau_args(method):
+    s = len(method.b)
+    A = np.ascontiguousarray(np.asarray(method.A, dtype=np.float64)).ravel()
+    c = np.ascontiguousarray(np.asarray(method.c, dtype=np.float64))
+    return s, A.ctypes.data_as(C.POINTER(C.c_double)), c.ctypes.data_as(C.POINTER(C.c_double)), (A, c)
+
+
+def _theta(setup, theta):
+    m = setup.closure_model
+    if m is None:
+        return float("nan")
+    if not getattr(m, "is_smagorinsky", False):
+        raise NotImplementedError("only smagorinsky_closure(setup) is fused into the B200 stepper")
+    if theta is None:
+        raise ValueError("closure_model is set: pass theta")
+    return float(theta)
+
+
+def timestep_(method, stepper, dt, theta=None, cache=None, p=None):
+    """timestep!(method, stepper, dt; theta, cache)  step_explicit_runge_kutta.jl:4-59.
+    `p` (optional scalar field) receives the last stage's multiplier."""
+    setup = stepper.setup
+    s, A, c, keep = _tableau_args(method)
+    _sync_stream(setup)
+    setup.ctx.call("insb200_rk_step", _ptr(_check(stepper.u, setup, True)), float(stepper.t), float(dt), s, A, c,
+                   _theta(setup, theta), _ptr(p) if p is not None else None)
+    T = setup.grid.T
+    t = T(stepper.t + T(method.c[-1]) * T(dt))
+    return create_stepper(method, setup, stepper.psolver, stepper.u, None, t, stepper.n + 1)
+
+
+def _rk_steps(method, setup, u, t, dt, nsteps, theta, ke_hist=False):
+    s, A, c, keep = _tableau_args(method)
+    tt = C.c_double(float(t))
+    ke = (C.c_double * (nsteps + 1))() if ke_hist else None
+    _sync_stream(setup)
+    setup.ctx.call("insb200_rk_steps", _ptr(_check(u, setup, True)), C.byref(tt), float(dt), int(nsteps), s, A, c,
+                   _theta(setup, theta), ke)
+    return setup.grid.T(tt.value), (np.array(ke[:]) if ke_hist else None)
+
+
+def get_state(stepper):
+    """get_state(stepper)  src/solver.jl:95-98"""
+    return SimpleNamespace(u=stepper.u, temp=None, t=stepper.t, n=stepper.n)
+
+
+def solve_unsteady(setup, tlims, ustart, tempstart=None, method=None, psolver=None, dt=None, dt_min=None,
+                   cfl=0.9, n_adapt_dt=1, docopy=True, processors=None, theta=None, cache=None):
+    """solve_unsteady(; setup, tlims, ustart, method, psolver, dt, dt_min, cfl, n_adapt_dt, docopy,
+    processors, theta, cache)  src/solver.jl:18-92.  Returns `(state, outputs)`.
+
+    `processors`: dict name -> processor (see processors.py).  With a fixed dt the steps between
+    two processor firings (their `nupdate`) run inside one `insb200_rk_steps` call, i.e. without
+    touching the reference layout or the host."""
+    T = setup.grid.T
+    if tempstart is not None:
+        raise NotImplementedError("temperature is outside the B200 hot path")
+    method = method or RKMethods.RK44(T=T)
+    psolver = psolver or default_psolver(setup)
+    u = ustart.clone() if docopy else ustart
+    tstart, tend = T(tlims[0]), T(tlims[1])
+    stepper = create_stepper(method, setup, psolver, u, None, tstart)
+    processors = processors or {}
+    state = Observable(get_state(stepper))
+    initialized = {k: v.initialize(state) for k, v in processors.items()}
+    nups = [getattr(v, "nupdate", 1) for v in processors.values()]
+    if dt is None:
+        cfl = T(cfl)
+        d = None
+        while stepper.t < tend:
+            if stepper.n % n_adapt_dt == 0:
+                d = T(cfl * get_cfl_timestep_(None, stepper.u, setup))
+                d = d if dt_min is None else max(d, T(dt_min))
+            d = min(d, T(tend - stepper.t))
+            stepper = timestep_(method, stepper, d, theta=theta, cache=cache)
+            state.set(get_state(stepper))
+    else:
+        nstep = int(round(float(tend - tstart) / float(dt)))
+        d = T((tend - tstart) / T(nstep))
+        chunk = int(np.gcd.reduce(nups)) if nups else nstep
+        chunk = max(1, min(chunk, nstep)) if nstep > 0 else 1
+        it = 0
+        while it < nstep:
+            m = min(chunk, nstep - it)
+            t, _ = _rk_steps(method, setup, stepper.u, stepper.t, d, m, theta)
+            it += m
+            stepper = create_stepper(method, setup, psolver, stepper.u, None, t, stepper.n + m)
+            state.set(get_state(stepper))
+    outputs = {k: processors[k].finalize(initialized[k], state) for k in processors}
+    return SimpleNamespace(u=stepper.u, temp=None, t=stepper.t, n=stepper.n), outputs
+
+
+def solve_unsteady_host(setup, tlims, ustart_host, method=None, dt=None, cfl=0.9, n_adapt_dt=1, theta=None,
+                        max_steps=0, ke_hist=0):
+    """solve_unsteady with HOST buffers through the single C-ABI call
+    `insb200_solve_unsteady_host`: `ustart_host` is a Julia-shaped NumPy array or a pinned CPU
+    tensor in device-field shape; it is advanced IN PLACE (H2D, all steps on the device, D2H).
+    Returns (nsteps, t_final, ke_history or None)."""
+    T = setup.grid.T
+    method = method or RKMethods.RK44(T=T)
+    s, A, c, keep = _tableau_args(method)
+    if isinstance(ustart_host, torch.Tensor):
+        if ustart_host.is_cuda or not ustart_host.is_contiguous():
+            raise TypeError("host entry point takes contiguous CPU memory")
+        ptr = C.c_void_p(ustart_host.data_ptr())
+    else:
+        if not (ustart_host.flags.f_contiguous and ustart_host.dtype == T):
+            raise TypeError("host array must be Fortran-contiguous with the setup's dtype")
+        ptr = C.c_void_p(ustart_host.ctypes.data)
+    ke = (C.c_double * ke_hist)() if ke_hist else None
+    ns, tout = C.c_int(), C.c_double()
+    _sync_stream(setup)
+    setup.ctx.call("insb200_solve_unsteady_host", ptr, float(tlims[0]), float(tlims[1]), -1.0 if dt is None else float(dt),
+                   float(cfl), int(n_adapt_dt), int(max_steps), s, A, c, _theta(setup, theta), ke, int(ke_hist),
+                   C.byref(ns), C.byref(tout))
+    return ns.value, T(tout.value), (np.array(ke[: min(ke_hist, ns.value + 1)]) if ke_hist else None)
+
+
+class Observable:
+    """Minimal stand-in for Observables.jl (`Observable(state)`, `on(f, obs)`, `obs[] = x`),
+    the hook processors listen on (src/processors.jl:39-40, src/solver.jl:49-50,68,78)."""
+
+    def __init__(self, value):
+        self.value = value
+        self.listeners = []
+
+    def on(self, f):
+        self.listeners.append(f)
+        return f
+
+    def set(self, value):
+        self.value = value
+        for f in self.listeners:
+            f(value)
+
+    def get(self):
+        return self.value
+
+
+# --------------------------------------------------------------------------------------------
+# slab helpers (host side of the multi-GPU decomposition: SURVEY 8e)
+# --------------------------------------------------------------------------------------------
+def slab_bounds(n_last, rank, nranks):
+    """[first, last) interior planes of the last axis owned by `rank`."""
+    if n_last % nranks:
+        raise ValueError("the last axis must be divisible by the number of ranks")
+    m = n_last // nranks
+    return rank * m, (rank + 1) * m
+
+
+def local_slab(a_global, D, rank, nranks):
+    """Cut the local ghosted slab (reference layout) of `rank` out of a GLOBAL ghosted Julia-shaped
+    array: interior planes [lo, hi) of axis D-1 plus one ghost plane each side."""
+    n_last = a_global.shape[D - 1] - 2
+    lo, hi = slab_bounds(n_last, rank, nranks)
+    idx = [slice(None)] * a_global.ndim
+    idx[D - 1] = slice(lo, hi + 2)
+    return np.asfortranarray(a_global[tuple(idx)])
+
+
+def gather_slabs(slabs, D):
+    """Inverse of local_slab for the interior planes; ghosts of the last axis are rebuilt
+    periodically.  `slabs`: list of local arrays ordered by rank."""
+    parts = []
+    for s in slabs:
+        idx = [slice(None)] * s.ndim
+        idx[D - 1] = slice(1, s.shape[D - 1] - 1)
+        parts.append(s[tuple(idx)])
+    core = np.concatenate(parts, axis=D - 1)
+    first = [slice(None)] * core.ndim
+    last = [slice(None)] * core.ndim
+    first[D - 1] = slice(0, 1)
+    last[D - 1] = slice(core.shape[D - 1] - 1, core.shape[D - 1])
+    return np.asfortranarray(np.concatenate((core[tuple(last)], core, core[tuple(first)]), axis=D - 1))

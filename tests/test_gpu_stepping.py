@@ -1,0 +1,183 @@
+"""GPU parity of the time stepper: `timestep!` / `solve_unsteady` on the CUDA path against the
+oracle, identical initial arrays (never "same seed").
+
+Tolerances are north_star's: relative L2 of u and p after N steps <= 1e-12 (Float64) / <= 1e-5
+(Float32), post-projection divergence at machine precision, kinetic-energy history to the same
+tolerance.  Float32 runs are compared with the Float32 oracle.
+"""
+import numpy as np
+import pytest
+
+from oracle import ins_oracle as o
+from tests.util import compare, make_pair
+
+pytestmark = pytest.mark.gpu
+TOL = {np.float64: 1e-12, np.float32: 1e-5}
+
+
+def tgv3(dim, x, y, z):
+    """examples/TaylorGreenVortex3D.jl:34-41"""
+    if dim == 1:
+        return np.sin(2 * np.pi * x) * np.cos(2 * np.pi * y) * np.sin(2 * np.pi * z) / 2
+    if dim == 2:
+        return -np.cos(2 * np.pi * x) * np.sin(2 * np.pi * y) * np.sin(2 * np.pi * z) / 2
+    return 0 * x * y * z
+
+
+def run_pair(n, T, nsteps, dt, Re=1000.0, force=False, smag=False, A=1.0, theta=None, seed=0):
+    import insb200 as ins
+
+    so, sc = make_pair(n, T, Re=Re, force=force, smag=smag)
+    u0 = o.random_field(so, A=A, kp=4 if min(n) < 32 else 10, rng=np.random.default_rng(seed))
+    # oracle
+    method_o = o.RK44(T)
+    st = o.create_stepper(method_o, so, o.psolver_spectral(so), u0.copy(order="F"))
+    ke_o = [o.total_kinetic_energy(u0, so)]
+    p_o = None
+    for _ in range(nsteps):
+        st, p_o = o.timestep(method_o, st, dt, theta=theta, return_p=True)
+        ke_o.append(o.total_kinetic_energy(st.u, so))
+    # CUDA, step by step through timestep! (exercises import/export every step)
+    method_c = ins.RKMethods.RK44(T=T)
+    ud = ins.to_device(u0, sc)
+    pd = ins.scalarfield(sc)
+    stc = ins.create_stepper(method_c, sc, ins.default_psolver(sc), ud)
+    ke_c = [ins.total_kinetic_energy(ud, sc)]
+    for _ in range(nsteps):
+        stc = ins.timestep_(method_c, stc, dt, theta=theta, p=pd)
+        ke_c.append(ins.total_kinetic_energy(stc.u, sc))
+    return ins, so, sc, u0, st, p_o, np.array(ke_o, dtype=np.float64), stc, pd, np.array(ke_c)
+
+
+@pytest.mark.parametrize("n,T,force,smag", [
+    ((32, 32), np.float64, False, False),
+    ((32, 32), np.float64, True, False),
+    ((32, 16), np.float32, True, False),
+    ((16, 16, 16), np.float64, False, False),
+    ((16, 32, 16), np.float32, False, False),
+    ((16, 16, 16), np.float64, False, True),
+    ((32, 32), np.float64, False, True),
+    ((16, 16, 32), np.float32, True, True),
+], ids=lambda v: str(v).replace(" ", ""))
+def test_rk44_steps_match_oracle(n, T, force, smag):
+    nsteps, dt = 10, 2e-3
+    theta = 0.17 if smag else None
+    ins, so, sc, u0, st, p_o, ke_o, stc, pd, ke_c = run_pair(n, T, nsteps, dt, force=force, smag=smag, theta=theta)
+    Ip = so.grid.Ip
+    tol = TOL[T]
+    compare("u after N steps", ins.to_host(stc.u), st.u, tol)       # ghosts included: valid on return
+    compare("p (last stage multiplier)", ins.to_host(pd)[Ip], p_o[Ip], tol * 20)
+    assert np.allclose(ke_c, ke_o, rtol=tol, atol=0), (ke_c, ke_o)
+    assert float(stc.t) == float(st.t) and stc.n == nsteps
+    div = ins.to_host(ins.divergence(stc.u, sc))[Ip]
+    assert np.abs(div).max() / max(n) < 100 * np.finfo(T).eps * max(np.abs(st.u).max(), 1e-30)
+
+
+def test_rk_steps_equals_repeated_timestep():
+    """insb200_rk_steps (device-resident loop) == repeated timestep! (reference layout every
+    step): bit-identical, and the kinetic-energy history it returns matches the reduction op."""
+    import insb200 as ins
+    from insb200.api import _rk_steps
+
+    so, sc = make_pair((16, 16, 16), np.float64)
+    u0 = o.random_field(so, kp=4, rng=np.random.default_rng(3))
+    m = ins.RKMethods.RK44()
+    a = ins.to_device(u0, sc)
+    st = ins.create_stepper(m, sc, None, a)
+    ke = [ins.total_kinetic_energy(a, sc)]
+    for _ in range(5):
+        st = ins.timestep_(m, st, 1e-3)
+        ke.append(ins.total_kinetic_energy(st.u, sc))
+    b = ins.to_device(u0, sc)
+    t, hist = _rk_steps(m, sc, b, 0.0, 1e-3, 5, None, ke_hist=True)
+    compare("rk_steps vs timestep!", ins.to_host(b), ins.to_host(a), 0, exact=True)
+    assert np.allclose(hist, ke, rtol=1e-14) and float(t) == float(st.t)
+
+
+def test_other_explicit_tableaux():
+    """Any explicit tableau is an argument: RK33P2 has a negative and an
+    off-diagonal entry, FE11 a single stage."""
+    import insb200 as ins
+
+    so, sc = make_pair((32, 32), np.float64)
+    u0 = o.random_field(so, kp=4, rng=np.random.default_rng(4))
+    for name, A, b, c in [("RK33P2", [[0, 0, 0], [1 / 3, 0, 0], [-1, 2, 0]], [0, 3 / 4, 1 / 4], [0, 1 / 3, 1]),
+                          ("FE11", [[0]], [1], [0])]:
+        mo = o.runge_kutta_method(A, b, c, 0)
+        st = o.create_stepper(mo, so, o.psolver_spectral(so), u0.copy(order="F"))
+        for _ in range(3):
+            st = o.timestep(mo, st, 2e-3)
+        mc = getattr(ins.RKMethods, name)()
+        stc = ins.create_stepper(mc, sc, None, ins.to_device(u0, sc))
+        for _ in range(3):
+            stc = ins.timestep_(mc, stc, 2e-3)
+        compare(name, ins.to_host(stc.u), st.u, 1e-12)
+
+
+def test_solve_unsteady_adaptive_config1_small():
+    """BASELINE config 1 (DecayingTurbulence2D, adaptive dt, cfl 0.9) at 64^2 Float64:
+    solve_unsteady through the host mirror AND through the host-buffer C entry point."""
+    import insb200 as ins
+
+    n = (64, 64)
+    so, sc = make_pair(n, np.float64, Re=4e3)
+    u0 = o.random_field(so, rng=np.random.default_rng(5))
+    state_o, out_o = o.solve_unsteady(so, (0.0, 0.02), u0, processors={"ke": lambda s: float(o.total_kinetic_energy(s.u, so))})
+    state_c, out_c = ins.solve_unsteady(sc, (0.0, 0.02), ins.to_device(u0, sc), processors={"ke": ins.energy_history(sc)})
+    assert state_c.n == state_o.n and np.isclose(float(state_c.t), float(state_o.t), rtol=1e-14)
+    compare("adaptive solve u", ins.to_host(state_c.u), state_o.u, 1e-11)
+    assert np.allclose(out_c["ke"][:, 1], out_o["ke"], rtol=1e-12)
+    uh = u0.copy(order="F")
+    ns, t, ke = ins.solve_unsteady_host(sc, (0.0, 0.02), uh, ke_hist=256)
+    assert ns == state_o.n
+    compare("host entry u", uh, state_o.u, 1e-11)
+    assert np.allclose(ke, out_o["ke"], rtol=1e-12)
+
+
+def test_taylor_green_3d_energy_config2():
+    """BASELINE config 2: TaylorGreenVortex3D periodic 128^3 Float64, Re=1e3, dt=1e-3.  Energy
+    check vs reference: (i) CUDA energy history == oracle history at 32^3 (same tolerance as u),
+    (ii) at the full 128^3 the inviscid limit conserves energy to O(dt^4) and the viscous run
+    dissipates monotonically with dE/dt ~ -2 nu * enstrophy (size-independent properties)."""
+    import insb200 as ins
+
+    T = np.float64
+    # (i) small, against the oracle
+    so, sc = make_pair((32, 32, 32), T, Re=1e3)
+    u0 = o.velocityfield(so, tgv3)
+    uc = ins.velocityfield(sc, tgv3)
+    compare("velocityfield", ins.to_host(uc), u0, 1e-12)
+    state_o, out_o = o.solve_unsteady(so, (0.0, 0.01), u0, dt=1e-3, processors={"ke": lambda s: float(o.total_kinetic_energy(s.u, so))})
+    state_c, out_c = ins.solve_unsteady(sc, (0.0, 0.01), uc, dt=1e-3, processors={"ke": ins.energy_history(sc)})
+    compare("TGV u", ins.to_host(state_c.u), state_o.u, 1e-12)
+    assert np.allclose(out_c["ke"][:, 1], out_o["ke"], rtol=1e-12)
+    # (ii) full size, properties
+    n = 128
+    x = tuple(np.linspace(0.0, 1.0, n + 1) for _ in range(3))
+    for Re, check in ((1e12, "conserve"), (1e3, "dissipate")):
+        s = ins.Setup(x, Re=Re)
+        u = ins.velocityfield(s, tgv3)
+        state, out = ins.solve_unsteady(s, (0.0, 0.02), u, dt=1e-3, processors={"ke": ins.energy_history(s)})
+        E = out["ke"][:, 1]
+        if check == "conserve":
+            assert abs(E[-1] - E[0]) / E[0] < 1e-10, E
+        else:
+            assert np.all(np.diff(E) < 0) and 1e-4 < (E[0] - E[-1]) / E[0] < 1e-1, E
+        div = ins.to_host(ins.divergence(state.u, s))[s.grid.Ip]
+        assert np.abs(div).max() / n < 100 * np.finfo(T).eps
+
+
+def test_processors_and_observers():
+    """processors API (src/processors.jl): timelogger, fieldsaver, observefield(:pressure)."""
+    import insb200 as ins
+
+    so, sc = make_pair((32, 32), np.float64)
+    u0 = o.random_field(so, kp=4, rng=np.random.default_rng(6))
+    lines = []
+    procs = {"log": ins.timelogger(sc, nupdate=2, sink=lines.append), "save": ins.fieldsaver(sc, nupdate=4),
+             "p": ins.observefield(sc, "pressure", nupdate=4)}
+    state, out = ins.solve_unsteady(sc, (0.0, 0.008), ins.to_device(u0, sc), dt=1e-3, processors=procs)
+    assert state.n == 8 and len(lines) == 4 and "umax" in lines[0]
+    assert [s.n for s in out["save"]] == [4, 8]
+    po = o.pressure(out["save"][-1].u, None, 0.0, so, o.psolver_spectral(so))
+    compare("observed pressure", out["p"][-1], po[so.grid.Ip], 1e-10)
