@@ -73,7 +73,8 @@ int insb200_apply_bc_p(insb200_ctx *ctx, void *p);
 int insb200_set_bodyforce(insb200_ctx *ctx, const void *f);
 
 /* momentum!(F, u, temp=nothing, t, setup): src/operators.jl:967-976 (fill! + convectiondiffusion!
- * :634-690 + applybodyforce! :861-879).  Ghosts of u must be valid; ghosts of F are set to 0. */
+ * :634-690 + applybodyforce! :861-879).  Ghosts of u must be valid; ghosts of F are 0, or the
+ * ghost values of the stored force field (`F .+= bodyforce` covers the whole array). */
 int insb200_momentum(insb200_ctx *ctx, void *F, const void *u, double t);
 
 /* convection! / diffusion! / convectiondiffusion! applied to a zero field:

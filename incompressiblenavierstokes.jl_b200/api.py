@@ -170,7 +170,10 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
                 sh = [1] * D
                 sh[b] = -1
                 xin.append(grid.xu[a][b].reshape(sh))
-            F[..., a] = np.broadcast_to(np.asarray(bodyforce(a + 1, *xin, T(0)), dtype=T), N)
+            # scalar broadcast `bodyforce.(a, x..., t)` like Julia: one scalar call per point (an
+            # array call could take NumPy's SIMD sin/cos path, which differs in the last bit)
+            val = np.vectorize(lambda *xs, _a=a: bodyforce(_a + 1, *xs, T(0)), otypes=[T])(*np.broadcast_arrays(*xin))
+            F[..., a] = val.astype(T)
         setup.bodyforce = to_device(F, setup)
         setup.issteadybodyforce = True
         ctx.call("insb200_set_bodyforce", _ptr(setup.bodyforce))

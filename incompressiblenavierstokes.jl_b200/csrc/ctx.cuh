@@ -86,6 +86,7 @@ struct insb200_ctx {
   void *ubuf[3] = {nullptr, nullptr, nullptr};          // rotating state buffers (compact vector)
   void *kbuf[INSB200_MAX_STAGES] = {nullptr};           // stage derivatives
   void *force = nullptr;                                // compact steady body force (nullable)
+  void *force_g = nullptr;                              // the same force in the reference layout (ghost values of F)
   void *sigma = nullptr;                                // compact symmetric tensor, D(D+1)/2 comps
   void *preal = nullptr;                                // compact scalar: FFT real buffer (+ ghost planes)
   void *pcplx = nullptr;                                // complex spectrum

@@ -244,7 +244,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->sigma, c->preal, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->preal, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -511,6 +511,11 @@ static int op_apply_bc(insb200_ctx *c, void *f, int nc) { return bc_fill<T, D>(c
 template <typename T, int D>
 static int op_set_bodyforce(insb200_ctx *c, const void *f) {
   INS_TRY(ensure_vec(c, &c->force));
+  // `F .+= bodyforce` (operators.jl:866) runs over the whole array: keep the ghost values too
+  i64 e = D;
+  for (int a = 0; a < D; a++) e *= c->nloc[a] + 2;
+  INS_TRY(dev_alloc(c, &c->force_g, (size_t)e * sizeof(T)));
+  INS_CUDA(c, cudaMemcpyAsync(c->force_g, f, (size_t)e * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
   return import_field<T, D>(c, c->force, f, D);
 }
 
@@ -538,8 +543,11 @@ static i64 ghosted_elems(const insb200_ctx *c) {
 
 template <typename T, int D>
 static int op_momentum(insb200_ctx *c, void *F, const void *u, int terms, bool with_force) {
-  // fill!(F, 0): ghosts of F stay zero (operators.jl:971)
-  INS_CUDA(c, cudaMemsetAsync(F, 0, (size_t)ghosted_elems(c) * D * sizeof(T), c->stream));
+  // fill!(F, 0) (operators.jl:971) then, with a force, `F .+= bodyforce` over the whole array
+  // (:866): ghosts of F are 0 resp. the ghost values of the stored force field
+  const size_t fb = (size_t)ghosted_elems(c) * D * sizeof(T);
+  if (with_force && c->force_g) INS_CUDA(c, cudaMemcpyAsync(F, c->force_g, fb, cudaMemcpyDeviceToDevice, c->stream));
+  else INS_CUDA(c, cudaMemsetAsync(F, 0, fb, c->stream));
   return launch_momentum<T, D>(c, view_ghosted<T>(c, F), view_ghosted_c<T>(c, u), geo_ghosted(c), terms, with_force);
 }
 
@@ -724,7 +732,11 @@ extern "C" int insb200_apply_bc_p(insb200_ctx *c, void *p) {
 extern "C" int insb200_set_bodyforce(insb200_ctx *c, const void *f) {
   API_PROLOG(c);
   if (!f) {
-    if (c->force) { INS_CUDA(c, cudaStreamSynchronize(c->stream)); cudaFree(c->force); c->force = nullptr; }
+    if (c->force) {
+      INS_CUDA(c, cudaStreamSynchronize(c->stream));
+      cudaFree(c->force); cudaFree(c->force_g);
+      c->force = nullptr; c->force_g = nullptr;
+    }
     return 0;
   }
   return DISPATCH(c, op_set_bodyforce, c, f);
