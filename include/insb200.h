@@ -55,6 +55,8 @@ int insb200_create(insb200_ctx **ctx, int D, const int *n, int dtype, const doub
                    int device, int rank, int nranks, const void *nccl_id);
 int insb200_destroy(insb200_ctx *ctx);
 const char *insb200_last_error(const insb200_ctx *ctx);
+/* All later calls enqueue on `cuda_stream` (a cudaStream_t; NULL = the CUDA legacy default stream).
+ * Until the first call a non-blocking stream owned by the ctx is used. */
 int insb200_set_stream(insb200_ctx *ctx, void *cuda_stream);
 int insb200_synchronize(insb200_ctx *ctx);
 
@@ -165,6 +167,12 @@ int insb200_reset_timers(insb200_ctx *ctx);
 /* Kernel variant switch for A/B runs: 0 = reference-structure kernels (one thread per cell,
  * direct global loads), 1 = tiled shared-memory kernels (default where available). */
 int insb200_set_variant(insb200_ctx *ctx, int variant);
+
+/* Tuning knobs for A/B runs (results are bit-identical for every setting):
+ *   "variant" 0/1 (as above), "tile_y" 8|16 (cells per block in y of the tiled stage kernel),
+ *   "zchunk" planes marched per block, "fuse_gradient" 0/1 (projection of stage i applied by the
+ *   loader of stage i+1 instead of a gradient kernel). */
+int insb200_set_param(insb200_ctx *ctx, const char *name, double value);
 
 /* Device memory owned by the ctx, in bytes. */
 long long insb200_workspace_bytes(const insb200_ctx *ctx);

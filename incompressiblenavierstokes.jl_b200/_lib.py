@@ -50,6 +50,7 @@ PROTOTYPES = {
     "insb200_timers": (c_int, [c_void_p, P(C.c_char_p), P(c_double), P(c_ll), c_int, P(c_int)]),
     "insb200_reset_timers": (c_int, [c_void_p]),
     "insb200_set_variant": (c_int, [c_void_p, c_int]),
+    "insb200_set_param": (c_int, [c_void_p, C.c_char_p, c_double]),
     "insb200_workspace_bytes": (c_ll, [c_void_p]),
 }
 

@@ -70,6 +70,9 @@ struct insb200_ctx {
   int device = 0;
   int rank = 0, nranks = 1;
   int variant = 1;
+  int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
+  int zchunk = 64;         // tiled stage kernel: planes marched per block
+  int fuse_gradient = 1;   // apply the projection of stage i in the loader of stage i+1
   cudaStream_t stream = nullptr;
   cudaStream_t own_stream = nullptr;
   ncclComm_t comm = nullptr;
@@ -89,6 +92,7 @@ struct insb200_ctx {
   void *force_g = nullptr;                              // the same force in the reference layout (ghost values of F)
   void *sigma = nullptr;                                // compact symmetric tensor, D(D+1)/2 comps
   void *preal = nullptr;                                // compact scalar: FFT real buffer (+ ghost planes)
+  void *preal2 = nullptr;                               // second scalar buffer (multiplier of the previous stage)
   void *pcplx = nullptr;                                // complex spectrum
   void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
   void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)

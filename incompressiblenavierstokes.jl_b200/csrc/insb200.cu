@@ -14,7 +14,7 @@
 namespace insb200 {
 thread_local std::string g_create_error;
 
-static const int kG = 1;  // ghost planes on the decomposed axis of compact buffers (nranks > 1)
+static const int kG = 2;  // ghost planes on the decomposed axis of compact buffers (nranks > 1)
 
 // ---- small host helpers ------------------------------------------------------------------------
 static inline dim3 cell_block() { return dim3(64, 4, 1); }
@@ -107,25 +107,26 @@ static double sinpi01(double x) {  // x in [0,1]; reduced so that multiples of 1
   if (cudaSetDevice((c)->device) != cudaSuccess) INS_FAIL((c), "cudaSetDevice failed")
 
 // ---- halo exchange along the decomposed axis (nranks > 1) ---------------------------------------
-// compact buffer with kG ghost planes each side; ncomp components of stride ccomp.
-// minus: fill my bottom ghost from prev's top interior plane; plus: my top ghost from next's bottom.
+// compact buffer with c->G ghost planes each side; ncomp components of stride ccomp.
+// wminus planes: my bottom ghosts <- prev's top interior planes; wplus: my top ghosts <- next's bottom.
 template <typename T>
-static int halo_compact(insb200_ctx *c, void *base, int ncomp, bool minus, bool plus) {
-  if (c->nranks == 1) return 0;
+static int halo_compact(insb200_ctx *c, void *base, int ncomp, int wminus, int wplus) {
+  if (c->nranks == 1 || (wminus <= 0 && wplus <= 0)) return 0;
   ScopedTimer tm(c, TM_HALO);
   const int prev = (c->rank + c->nranks - 1) % c->nranks, next = (c->rank + 1) % c->nranks;
   const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
-  const i64 pl = c->cplane, nl = c->nloc[c->last];
+  const i64 pl = c->cplane, nl = c->nloc[c->last], G = c->G;
+  if (wminus > G || wplus > G || wminus > nl || wplus > nl) INS_FAIL(c, "halo width exceeds the ghost planes");
   INS_NCCL(c, ncclGroupStart());
   for (int q = 0; q < ncomp; q++) {
     T *b = (T *)base + q * c->ccomp;
-    if (minus) {  // top interior plane -> next ; recv bottom ghost <- prev
-      INS_NCCL(c, ncclSend(b + (kG + nl - 1) * pl, pl, dt, next, c->comm, c->stream));
-      INS_NCCL(c, ncclRecv(b + (kG - 1) * pl, pl, dt, prev, c->comm, c->stream));
+    if (wminus > 0) {  // top interior planes -> next ; recv bottom ghosts <- prev
+      INS_NCCL(c, ncclSend(b + (G + nl - wminus) * pl, wminus * pl, dt, next, c->comm, c->stream));
+      INS_NCCL(c, ncclRecv(b + (G - wminus) * pl, wminus * pl, dt, prev, c->comm, c->stream));
     }
-    if (plus) {  // bottom interior plane -> prev ; recv top ghost <- next
-      INS_NCCL(c, ncclSend(b + kG * pl, pl, dt, prev, c->comm, c->stream));
-      INS_NCCL(c, ncclRecv(b + (kG + nl) * pl, pl, dt, next, c->comm, c->stream));
+    if (wplus > 0) {  // bottom interior planes -> prev ; recv top ghosts <- next
+      INS_NCCL(c, ncclSend(b + G * pl, wplus * pl, dt, prev, c->comm, c->stream));
+      INS_NCCL(c, ncclRecv(b + (G + nl) * pl, wplus * pl, dt, next, c->comm, c->stream));
     }
   }
   INS_NCCL(c, ncclGroupEnd());
@@ -244,7 +245,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->force_g, c->sigma, c->preal, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -261,7 +262,7 @@ extern "C" const char *insb200_last_error(const insb200_ctx *c) {
 
 extern "C" int insb200_set_stream(insb200_ctx *c, void *s) {
   CHECK_CTX(c);
-  c->stream = s ? (cudaStream_t)s : c->own_stream;
+  c->stream = (cudaStream_t)s;  // NULL = the CUDA legacy default stream (not the ctx-owned one)
   if (c->plans) {
     cufftHandle hs[] = {c->plan_fwd, c->plan_inv, c->plan_fwd_in, c->plan_inv_in, c->plan_last};
     for (cufftHandle hd : hs) if (hd) INS_CUFFT(c, cufftSetStream(hd, c->stream));
@@ -563,15 +564,15 @@ static T eddy_const(const insb200_ctx *c, double theta) {
 
 // sigma(u) on all local p-cells into c->sigma, then its halo on the decomposed axis
 template <typename T, int D>
-static int compute_sigma(insb200_ctx *c, View<const T> u, Geo gu, double theta) {
+static int compute_sigma(insb200_ctx *c, View<const T> u, Geo gu, double theta, const T *pin = nullptr) {
   INS_TRY(ensure_sigma(c));
   {
     ScopedTimer tm(c, TM_SMAGTENSOR);
-    k_smagtensor<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_compact<T>(c, c->sigma), u, gu,
+    k_smagtensor<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_compact<T>(c, c->sigma), u, pin, gu,
                                                                         eddy_const<T>(c, theta), make_rh<T>(c));
     CHECK_LAUNCH(c);
   }
-  return halo_compact<T>(c, c->sigma, D * (D + 1) / 2, true, true);
+  return halo_compact<T>(c, c->sigma, D * (D + 1) / 2, 1, 1);
 }
 
 template <typename T, int D>
@@ -642,7 +643,7 @@ static int project_view(insb200_ctx *c, View<T> u, Geo gu) {
   View<const T> uc{u.p, u.sy, u.sz, u.sc};
   INS_TRY((launch_divergence<T, D>(c, view_compact<T>(c, c->preal), uc, gu, true)));
   INS_TRY((poisson_solve<T, D>(c)));
-  INS_TRY((halo_compact<T>(c, c->preal, 1, false, true)));
+  INS_TRY((halo_compact<T>(c, c->preal, 1, 0, 1)));
   return launch_gradient<T, D, 1>(c, u, view_compact_c<T>(c, c->preal), geo_compact(c));
 }
 
@@ -665,7 +666,7 @@ static int op_pressure(insb200_ctx *c, void *p, const void *u) {
   INS_TRY(ensure_vec(c, &c->fwork));
   // momentum!(F,u) -> apply_bc_u!(F; dudt) (periodic: wrap / halo) -> divergence -> scale -> solve -> bc
   INS_TRY((launch_momentum<T, D>(c, view_compact<T>(c, c->fwork), view_ghosted_c<T>(c, u), geo_ghosted(c), 3, true)));
-  INS_TRY((halo_compact<T>(c, c->fwork, D, true, false)));
+  INS_TRY((halo_compact<T>(c, c->fwork, D, 1, 0)));
   INS_TRY((launch_divergence<T, D>(c, view_compact<T>(c, c->preal), view_compact_c<T>(c, c->fwork), geo_compact(c), true)));
   INS_TRY((poisson_solve<T, D>(c)));
   return export_p<T, D>(c, p);
@@ -818,10 +819,56 @@ extern "C" int insb200_maxabs(insb200_ctx *c, const void *u, double *m) {
 }
 
 namespace insb200 {
-// fused momentum + stage combination; variant 0 = one thread per cell, 1 = tiled (tiled.cuh)
+// ---- tiled 3-D stage kernel (tiled.cuh) ----------------------------------------------------------
+template <typename T, int D>
+static bool tiled_stage_supported(const insb200_ctx *c) {
+  if (D != 3 || c->variant < 1) return false;
+  const int ty = c->tile_y == 16 ? 16 : 8;
+  return c->nloc[0] % 32 == 0 && c->nloc[1] % ty == 0 && c->nloc[2] >= 2;
+}
+
+template <typename T, bool SMAG, bool PGRAD, int TX, int TY>
+static int launch_stage3d(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh) {
+  typedef Tile3<TX, TY> TL;
+  const size_t smem = (size_t)(12 * TL::NP + 2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T);
+  auto kern = k_stage3d<T, SMAG, PGRAD, TX, TY>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  dim3 grd(c->nloc[0] / TX, c->nloc[1] / TY, (c->nloc[2] + zc - 1) / zc), blk(TX, TY, 1);
+  kern<<<grd, blk, smem, c->stream>>>(a, g, visc, rh, volume<T>(c), zc);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D>
+static int launch_stage_tiled(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, bool smag) {
+  if (D != 3) INS_FAIL(c, "tiled stage kernel is 3-D only");
+  const bool pg = a.pin != nullptr;
+#define LS(SM, PG)                                                                            \
+  (c->tile_y == 16 ? launch_stage3d<T, SM, PG, 32, 16>(c, a, g, visc, rh) : launch_stage3d<T, SM, PG, 32, 8>(c, a, g, visc, rh))
+  if (smag) return pg ? LS(true, true) : LS(true, false);
+  return pg ? LS(false, true) : LS(false, false);
+#undef LS
+}
+
+// divergence of u' on the first plane of every z-chunk of the tiled kernel (needs the minus-side halo of u')
+template <typename T>
+static int launch_divergence_planes(insb200_ctx *c, T *out, const T *u, Geo g) {
+  ScopedTimer tm(c, TM_DIVERGENCE);
+  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  dim3 blk(64, 4, 1), grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 3) / 4, (c->nloc[2] + zc - 1) / zc);
+  k_divergence_planes<T><<<grd, blk, 0, c->stream>>>(out, u, c->csy, c->csz, c->ccomp, g, make_rh<T>(c), volume<T>(c), zc);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// fused momentum + stage combination, one thread per cell (any D, any n)
 template <typename T, int D>
 static int launch_stage(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, bool smag) {
-  if (c->variant >= 1 && tiled_stage_supported<T, D>(c, g)) return launch_stage_tiled<T, D>(c, a, g, visc, rh, smag);
   dim3 grd = cell_grid(c->nloc), blk = cell_block();
   if (smag) k_momentum_stage<T, D, true><<<grd, blk, 0, c->stream>>>(a, g, visc, rh);
   else k_momentum_stage<T, D, false><<<grd, blk, 0, c->stream>>>(a, g, visc, rh);
@@ -863,21 +910,29 @@ static int ensure_rk(insb200_ctx *c, const Tableau &tb, bool smag) {
 }
 
 // one timestep!: state in ubuf[0] (compact), result in ubuf[0] (buffers rotated).
+//
+// Tiled path (3-D, tile-aligned n): per stage ONE kernel produces k_i, u' and the Poisson right-hand
+// side; the projection u = u' - grad p of stages 1..s-1 is applied by the NEXT stage's loader, so only
+// the last stage runs the gradient kernel.  Otherwise: stage kernel, divergence, solve, gradient.
 template <typename T, int D>
 static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
   const bool smag = !std::isnan(theta);
   const Geo g = geo_compact(c);
   const T visc = T(1) / T(c->Re);
   const Rh<T> rh = make_rh<T>(c);
+  const bool tiled = tiled_stage_supported<T, D>(c);
+  const bool fuse_grad = tiled && c->fuse_gradient;
+  const i64 goff = (i64)c->G * c->cplane;
+  T *pr = (T *)c->preal + goff;
   int cur = 0;
+  bool pending = false;  // ubuf[cur] holds u' of the previous stage, its gradient correction is still in preal
   for (int i = 0; i < tb.s; i++) {
     const int nxt = (cur == 1) ? 2 : 1;
     // apply_bc_u! before momentum (step_explicit_runge_kutta.jl:19): wrap by index, halos over NCCL
-    INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, true, true)));
-    if (smag) INS_TRY((compute_sigma<T, D>(c, view_compact_c<T>(c, c->ubuf[cur]), g, theta)));
+    if (!pending) INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, 1, 1)));  // (pending: exchanged after the stage kernel)
+    if (smag) INS_TRY((compute_sigma<T, D>(c, view_compact_c<T>(c, c->ubuf[cur]), g, theta, pending ? pr : nullptr)));
     StageArgs<T> a;
     memset(&a, 0, sizeof a);
-    const i64 goff = (i64)c->G * c->cplane;
     a.u = (const T *)c->ubuf[cur] + goff;
     a.u0 = (const T *)c->ubuf[0] + goff;
     a.nk = 0;
@@ -892,14 +947,45 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
     a.unew = (T *)c->ubuf[nxt] + goff;
     a.force = c->force ? (const T *)c->force + goff : nullptr;
     a.sigma = smag ? (const T *)c->sigma + goff : nullptr;
+    a.pin = pending ? pr : nullptr;
+    a.div = tiled ? pr : nullptr;
     a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp; a.ssc = c->ccomp;
-    {
-      ScopedTimer tm(c, TM_STAGE);
-      INS_TRY((launch_stage<T, D>(c, a, g, visc, rh, smag)));
+    if (tiled) {
+      // with a pending gradient the kernel reads p while it writes the new right-hand side into the
+      // same scalar buffer: keep the multiplier in a second buffer
+      if (pending) {
+        INS_TRY(dev_alloc(c, &c->preal2, (size_t)c->ccomp * sizeof(T)));
+        std::swap(c->preal, c->preal2);
+        pr = (T *)c->preal + goff;
+        a.pin = (const T *)c->preal2 + goff;
+        a.div = pr;
+      }
+      {
+        ScopedTimer tm(c, TM_STAGE);
+        INS_TRY((launch_stage_tiled<T, D>(c, a, g, visc, rh, smag)));
+      }
+      // u' halos: the minus side for the chunk-first planes of the divergence, both for the next stage
+      INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, 1, 1)));
+      INS_TRY((launch_divergence_planes<T>(c, pr, (const T *)c->ubuf[nxt] + goff, g)));
+      INS_TRY((poisson_solve<T, D>(c)));
+      const bool last = i == tb.s - 1;
+      if (fuse_grad && !last) {
+        INS_TRY((halo_compact<T>(c, c->preal, 1, 1, 2)));
+        pending = true;
+      } else {
+        INS_TRY((halo_compact<T>(c, c->preal, 1, 0, 1)));
+        INS_TRY((launch_gradient<T, D, 1>(c, view_compact<T>(c, c->ubuf[nxt]), view_compact_c<T>(c, c->preal), g)));
+        pending = false;
+      }
+    } else {
+      {
+        ScopedTimer tm(c, TM_STAGE);
+        INS_TRY((launch_stage<T, D>(c, a, g, visc, rh, smag)));
+      }
+      // apply_bc_u! + project! (:48-49): only the minus-side halo of u' is consumed by the divergence
+      INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, 1, 0)));
+      INS_TRY((project_view<T, D>(c, view_compact<T>(c, c->ubuf[nxt]), g)));
     }
-    // apply_bc_u! + project! (:48-49): only the minus-side halo of u' is consumed by the divergence
-    INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, true, false)));
-    INS_TRY((project_view<T, D>(c, view_compact<T>(c, c->ubuf[nxt]), g)));
     cur = nxt;
   }
   std::swap(c->ubuf[0], c->ubuf[cur]);
@@ -908,7 +994,7 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
 
 template <typename T, int D>
 static int reduce_compact(insb200_ctx *c, double *out4) {
-  INS_TRY((halo_compact<T>(c, c->ubuf[0], D, true, false)));
+  INS_TRY((halo_compact<T>(c, c->ubuf[0], D, 1, 0)));
   return reduce_view<T, D>(c, view_compact_c<T>(c, c->ubuf[0]), geo_compact(c), out4);
 }
 
@@ -1078,5 +1164,17 @@ extern "C" int insb200_timers(insb200_ctx *c, const char **names, double *ms, lo
 extern "C" int insb200_set_variant(insb200_ctx *c, int variant) {
   if (!c) return 1;
   c->variant = variant;
+  return 0;
+}
+extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value) {
+  if (!c) return 1;
+  if (!name) INS_FAIL(c, "parameter name is NULL");
+  const std::string k(name);
+  const int v = (int)value;
+  if (k == "variant") c->variant = v;
+  else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
+  else if (k == "zchunk") { if (v < 2) INS_FAIL(c, "zchunk must be >= 2"); c->zchunk = v; }
+  else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
+  else INS_FAIL(c, "unknown parameter: " + k);
   return 0;
 }

@@ -49,6 +49,22 @@ struct Acc {  // read accessor of a multi-component field at a stencil
   }
 };
 
+// read accessor of u = u' - grad p (applypressure! fused into the read, operators.jl:225-233);
+// the stencil `s` has radius 2 because p is read one cell beyond the velocity stencil.
+template <typename T, int D>
+struct GradAcc {
+  const T *__restrict__ u;
+  const T *__restrict__ p;
+  i64 sc;
+  T rh[3];
+  const Sten<D, 2> &s;
+  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
+    const T p0 = __ldg(p + s.at(dx, dy, dz));
+    const T p1 = __ldg(p + s.at(dx + (c == 0), dy + (c == 1), dz + (c == 2)));
+    return __ldg(u + c * sc + s.at(dx, dy, dz)) - (p1 - p0) * rh[c];
+  }
+};
+
 // ---------------------------------------------------------------------------------------------
 // convection_diffusion_kernel!  src/operators.jl:647-690 (also convection_kernel! :392-415 and
 // diffusion_kernel! :551-573 through the CONV / DIFF switches), one component `a` at one cell.
@@ -246,6 +262,8 @@ struct StageArgs {
   T *unew;
   const T *force;   // nullable (compact)
   const T *sigma;   // nullable (compact, ghost planes valid when not wrapped)
+  const T *pin;     // tiled kernels with PGRAD: multiplier p of the previous stage, u = u' - grad p on load
+  T *div;           // tiled kernels: nullable, receives divergence(unew) * Omega (the Poisson right-hand side)
   i64 sy, sz, sc;   // strides shared by all compact vector buffers
   i64 ssc;          // component stride of sigma
 };
@@ -271,13 +289,20 @@ __global__ void k_momentum_stage(StageArgs<T> A, Geo g, T visc, Rh<T> rh) {
 }
 
 // smagtensor! on all local p-cells (src/operators.jl:1135-1151) into the compact sigma buffer
+// `pin` non-null: the velocity is u - grad pin (projection of the previous stage fused into the read)
 template <typename T, int D>
-__global__ void k_smagtensor(View<T> sg, View<const T> u, Geo g, T c_eddy, Rh<T> rh) {
+__global__ void k_smagtensor(View<T> sg, View<const T> u, const T *__restrict__ pin, Geo g, T c_eddy, Rh<T> rh) {
   INS_CELL_IDX(g)
-  Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
-  Acc<T, D, 1> U{u.p, u.sc, s};
   T sig[6];
-  smag_sigma<T, D>(U, c_eddy, rh.v, sig);
+  if (pin) {
+    Sten<D, 2> s(g, u.sy, u.sz, i, j, k);
+    GradAcc<T, D> U{u.p, pin, u.sc, {rh.v[0], rh.v[1], rh.v[2]}, s};
+    smag_sigma<T, D>(U, c_eddy, rh.v, sig);
+  } else {
+    Sten<D, 1> s(g, u.sy, u.sz, i, j, k);
+    Acc<T, D, 1> U{u.p, u.sc, s};
+    smag_sigma<T, D>(U, c_eddy, rh.v, sig);
+  }
   const i64 o = k * sg.sz + j * sg.sy + i;
 #pragma unroll
   for (int c = 0; c < D * (D + 1) / 2; c++) sg.p[c * sg.sc + o] = sig[c];
