@@ -8,9 +8,16 @@
 //     either wrapped (nranks == 1) or padded with G ghost planes filled over NCCL (nranks > 1).
 //     Row pitch n*sizeof(T) is a multiple of 16 B for every admissible n (n even and, for the
 //     vector paths, n % 4 == 0), so rows can be moved with 128-bit loads / bulk copies.
-//   The RK state (ustart, stage buffers, k_i, sigma, FFT buffers) lives in the compact layout;
-//   the reference layout is touched once on entry and once on exit of a stepping call.
+//   padded layout (internal, 3-D): (PX, PY, PZ) with REAL ghost cells -- gm = 2 layers on the minus
+//     side and gp = 3 on the plus side in y and z, 64 B (left) + 64 B (right) in x -- so PX*sizeof(T)
+//     is a multiple of 128 B and the interior origin is 64-B aligned.  Any tile + halo is one
+//     in-bounds TMA box (tma_stage.cuh); the ghosts are refreshed by k_fill_ghosts (x, y, and z on one
+//     rank) or by NCCL plane exchange (z, nranks > 1).  The one-thread-per-cell kernels address the
+//     same buffers through (origin, strides) and wrap indices instead of reading ghosts.
+//   The RK state (ustart, stage buffers, k_i, s, FFT buffers) lives in the compact (2-D) or padded
+//   (3-D) layout; the reference layout is touched once on entry and once on exit of a stepping call.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <cufft.h>
 #include <nccl.h>
@@ -19,7 +26,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/insb200.h"
@@ -69,9 +78,13 @@ struct insb200_ctx {
   double Re = 1;
   int device = 0;
   int rank = 0, nranks = 1;
-  int variant = 1;
+  int variant = 2;         // 0: one thread per cell, 1: LDG-tiled stage kernel, 2: TMA plane pipeline (3-D)
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
   int zchunk = 64;         // tiled stage kernel: planes marched per block
+  int padded = 0;          // 1: padded layout with real ghost cells (3-D)
+  int org[3] = {0, 0, 0};  // interior origin inside the padded box (elements)
+  int ext[3] = {1, 1, 1};  // padded extents PX, PY, PZ
+  int gm = 0, gp = 0;      // ghost layers kept valid on the minus / plus side (y, z; x has more room)
   int fuse_gradient = 1;   // apply the projection of stage i in the loader of stage i+1
   cudaStream_t stream = nullptr;
   cudaStream_t own_stream = nullptr;
@@ -84,6 +97,7 @@ struct insb200_ctx {
   insb200::i64 cplane = 0;            // elements of one last-axis plane
   insb200::i64 ccomp = 0;             // elements per component incl. ghost planes
   insb200::i64 cint = 0;              // interior elements per component
+  insb200::i64 corg = 0;              // offset of interior cell (0,0,0) from the buffer start
 
   // workspaces (device), element type = dtype
   void *ubuf[3] = {nullptr, nullptr, nullptr};          // rotating state buffers (compact vector)
@@ -91,6 +105,8 @@ struct insb200_ctx {
   void *force = nullptr;                                // compact steady body force (nullable)
   void *force_g = nullptr;                              // the same force in the reference layout (ghost values of F)
   void *sigma = nullptr;                                // compact symmetric tensor, D(D+1)/2 comps
+  void *sbuf = nullptr;                                 // closure term s = div sigma (vector, TMA path)
+  std::map<std::tuple<const void *, int, int>, CUtensorMap> tmaps;  // (buffer, ncomp, box rows) -> descriptor
   void *preal = nullptr;                                // compact scalar: FFT real buffer (+ ghost planes)
   void *preal2 = nullptr;                               // second scalar buffer (multiplier of the previous stage)
   void *pcplx = nullptr;                                // complex spectrum

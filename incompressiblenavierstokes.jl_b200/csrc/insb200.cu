@@ -10,6 +10,7 @@
 #include "ctx.cuh"
 #include "stencil.cuh"
 #include "tiled.cuh"
+#include "tma_stage.cuh"
 
 namespace insb200 {
 thread_local std::string g_create_error;
@@ -57,7 +58,7 @@ static View<T> view_compact(const insb200_ctx *c, void *base) {
   v.sy = c->csy;
   v.sz = c->csz;
   v.sc = c->ccomp;
-  v.p = (T *)base + (i64)c->G * c->cplane;
+  v.p = (T *)base + c->corg;
   return v;
 }
 template <typename T>
@@ -81,6 +82,7 @@ static T volume(const insb200_ctx *c) {  // (dx*dy)*dz in T  (operators.jl:92)
 
 static int dev_alloc(insb200_ctx *c, void **p, size_t bytes) {
   if (*p) return 0;
+  bytes += 256;  // slack: TMA boxes / neighbour reads may touch a few elements past the last row
   INS_CUDA(c, cudaMalloc(p, bytes));
   INS_CUDA(c, cudaMemsetAsync(*p, 0, bytes, c->stream));
   c->ws_bytes += (i64)bytes;
@@ -116,7 +118,8 @@ static int halo_compact(insb200_ctx *c, void *base, int ncomp, int wminus, int w
   const int prev = (c->rank + c->nranks - 1) % c->nranks, next = (c->rank + 1) % c->nranks;
   const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
   const i64 pl = c->cplane, nl = c->nloc[c->last], G = c->G;
-  if (wminus > G || wplus > G || wminus > nl || wplus > nl) INS_FAIL(c, "halo width exceeds the ghost planes");
+  const i64 Gp = c->padded ? c->gp : G;
+  if (wminus > G || wplus > Gp || wminus > nl || wplus > nl) INS_FAIL(c, "halo width exceeds the ghost planes");
   INS_NCCL(c, ncclGroupStart());
   for (int q = 0; q < ncomp; q++) {
     T *b = (T *)base + q * c->ccomp;
@@ -199,12 +202,29 @@ extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype,
   for (int a = 0; a < D; a++) { c->nglob[a] = n[a]; c->nloc[a] = n[a]; c->h[a] = h[a]; }
   c->nloc[c->last] = n[c->last] / nranks;
   c->off_last = rank * c->nloc[c->last];
-  c->G = nranks > 1 ? kG : 0;
-  c->csy = c->nloc[0];
-  c->csz = D == 3 ? (i64)c->nloc[0] * c->nloc[1] : 0;
-  c->cplane = D == 3 ? c->csz : c->csy;
-  c->cint = (i64)c->nloc[0] * c->nloc[1] * c->nloc[2];
-  c->ccomp = c->cint + 2 * (i64)c->G * c->cplane;
+  if (D == 3) {
+    // padded layout (ctx.cuh): 64 B of x margin each side, gm/gp ghost layers in y and z
+    const int es = dtype == INSB200_F64 ? 8 : 4;
+    c->padded = 1;
+    c->gm = 2; c->gp = 3;
+    c->org[0] = 64 / es; c->org[1] = c->gm; c->org[2] = c->gm;
+    c->ext[0] = c->nloc[0] + 128 / es; c->ext[1] = c->nloc[1] + c->gm + c->gp; c->ext[2] = c->nloc[2] + c->gm + c->gp;
+    c->G = c->gm;
+    c->csy = c->ext[0];
+    c->csz = (i64)c->ext[0] * c->ext[1];
+    c->cplane = c->csz;
+    c->cint = (i64)c->nloc[0] * c->nloc[1] * c->nloc[2];
+    c->ccomp = c->csz * c->ext[2];
+    c->corg = c->org[0] + c->org[1] * c->csy + c->org[2] * c->csz;
+  } else {
+    c->G = nranks > 1 ? kG : 0;
+    c->csy = c->nloc[0];
+    c->csz = 0;
+    c->cplane = c->csy;
+    c->cint = (i64)c->nloc[0] * c->nloc[1];
+    c->ccomp = c->cint + 2 * (i64)c->G * c->cplane;
+    c->corg = (i64)c->G * c->cplane;
+  }
   c->nxh = n[0] / 2 + 1;
   c->kxc = (c->nxh + nranks - 1) / nranks;
   c->kx0 = std::min(rank * c->kxc, c->nxh);
@@ -245,7 +265,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->force_g, c->sigma, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -302,8 +322,12 @@ static int ensure_fft(insb200_ctx *c) {
       INS_CUFFT(c, cufftPlan2d(&c->plan_fwd, c->nloc[1], c->nloc[0], f32 ? CUFFT_R2C : CUFFT_D2Z));
       INS_CUFFT(c, cufftPlan2d(&c->plan_inv, c->nloc[1], c->nloc[0], f32 ? CUFFT_C2R : CUFFT_Z2D));
     } else {
-      INS_CUFFT(c, cufftPlan3d(&c->plan_fwd, c->nloc[2], c->nloc[1], c->nloc[0], f32 ? CUFFT_R2C : CUFFT_D2Z));
-      INS_CUFFT(c, cufftPlan3d(&c->plan_inv, c->nloc[2], c->nloc[1], c->nloc[0], f32 ? CUFFT_C2R : CUFFT_Z2D));
+      // advanced data layout: the real side is the interior of the padded scalar buffer
+      int nn[3] = {c->nloc[2], c->nloc[1], c->nloc[0]};
+      int remb[3] = {c->ext[2], c->ext[1], c->ext[0]};
+      int cemb[3] = {c->nloc[2], c->nloc[1], c->nxh};
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd, 3, nn, remb, 1, (int)c->ccomp, cemb, 1, cemb[0] * cemb[1] * cemb[2], f32 ? CUFFT_R2C : CUFFT_D2Z, 1));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv, 3, nn, cemb, 1, cemb[0] * cemb[1] * cemb[2], remb, 1, (int)c->ccomp, f32 ? CUFFT_C2R : CUFFT_Z2D, 1));
     }
     INS_CUFFT(c, cufftSetStream(c->plan_fwd, c->stream));
     INS_CUFFT(c, cufftSetStream(c->plan_inv, c->stream));
@@ -315,8 +339,11 @@ static int ensure_fft(insb200_ctx *c) {
     INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
     if (D == 3) {
       int nn[2] = {c->nloc[1], c->nloc[0]};
-      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
-      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
+      int remb[2] = {c->ext[1], c->ext[0]};
+      int cemb[2] = {c->nloc[1], c->nxh};
+      const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxh;
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
     } else {
       int nn[1] = {c->nloc[0]};
       INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 1, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[1]));
@@ -340,6 +367,60 @@ static int ensure_fft(insb200_ctx *c) {
 static int ensure_vec(insb200_ctx *c, void **p) { return dev_alloc(c, p, (size_t)c->ccomp * c->D * esize(c)); }
 static int ensure_sigma(insb200_ctx *c) {
   return dev_alloc(c, &c->sigma, (size_t)c->ccomp * (c->D * (c->D + 1) / 2) * esize(c));
+}
+
+// ---- padded layout: ghost refresh and TMA descriptors ---------------------------------------------
+// periodic ghosts of a padded buffer with nc components: x and y always, z by index wrap on one rank,
+// by plane exchange with the ring neighbours otherwise (wm / wp planes on the minus / plus side)
+template <typename T>
+static int fill_ghosts(insb200_ctx *c, void *base, int nc, int wm, int wp) {
+  if (!c->padded) return 0;
+  {
+    ScopedTimer tm(c, TM_BC);
+    const int gm = c->gm, gp = c->gp, gw = gm + gp;
+    const int n0 = c->nloc[0], n1 = c->nloc[1], n2 = c->nloc[2];
+    const int fill_z = c->nranks == 1;
+    const i64 cntA = fill_z ? (i64)gw * (n0 + gw) * (n1 + gw) : 0;
+    const i64 cntB = (i64)n2 * gw * (n0 + gw), cntC = (i64)n2 * n1 * gw;
+    const i64 tot = cntA + cntB + cntC;
+    dim3 grd((unsigned)((tot + 255) / 256), nc, 1);
+    k_fill_ghosts<T><<<grd, 256, 0, c->stream>>>((T *)base + c->corg, c->csy, c->csz, c->ccomp, n0, n1, n2, gm, gp, fill_z, cntA,
+                                                cntB, cntC);
+    CHECK_LAUNCH(c);
+  }
+  return halo_compact<T>(c, base, nc, wm, wp);
+}
+
+typedef CUresult (*PFN_tmap_encode)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// descriptor of a padded buffer with nc components, box = (box_x, box_y, 1, nc)
+static int get_tmap(insb200_ctx *c, const void *base, int nc, int box_x, int box_y, CUtensorMap *out) {
+  auto key = std::make_tuple(base, nc, box_y);
+  auto it = c->tmaps.find(key);
+  if (it != c->tmaps.end()) { *out = it->second; return 0; }
+  static PFN_tmap_encode enc = nullptr;
+  if (!enc) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    INS_CUDA(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+    if (!fn || qr != cudaDriverEntryPointSuccess) INS_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
+    enc = (PFN_tmap_encode)fn;
+  }
+  const cuuint64_t es = esize(c);
+  cuuint64_t dims[4] = {(cuuint64_t)c->ext[0], (cuuint64_t)c->ext[1], (cuuint64_t)c->ext[2], (cuuint64_t)nc};
+  cuuint64_t strides[3] = {(cuuint64_t)c->csy * es, (cuuint64_t)c->csz * es, (cuuint64_t)c->ccomp * es};
+  cuuint32_t box[4] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1u, (cuuint32_t)nc};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUtensorMap tm;
+  CUresult r = enc(&tm, c->dtype == INSB200_F64 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4,
+                   const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) INS_FAIL(c, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+  c->tmaps[key] = tm;
+  *out = tm;
+  return 0;
 }
 
 // ---- layout conversion ----------------------------------------------------------------------------
@@ -399,7 +480,7 @@ template <typename T, int D>
 static int poisson_solve(insb200_ctx *c) {
   INS_TRY(ensure_fft(c));
   typedef typename std::conditional<sizeof(T) == 4, cufftComplex, cufftDoubleComplex>::type C;
-  T *pr = (T *)c->preal + (i64)c->G * c->cplane;
+  T *pr = (T *)c->preal + c->corg;
   C *S = (C *)c->pcplx;
   const double ntot = (double)c->nglob[0] * c->nglob[1] * (D == 3 ? c->nglob[2] : 1);
   const T invN = T(1) / T(ntot);
@@ -866,6 +947,75 @@ static int launch_divergence_planes(insb200_ctx *c, T *out, const T *u, Geo g) {
   return 0;
 }
 
+// ---- TMA plane-pipeline kernels (tma_stage.cuh): padded 3-D layout ---------------------------------
+static const int kTX = 32, kTY = 16, kNS = 4;
+
+template <typename T, int D>
+static bool tma_supported(const insb200_ctx *c) {
+  return D == 3 && c->padded && c->variant >= 2 && c->nloc[0] % kTX == 0 && c->nloc[1] % kTY == 0 && c->nloc[2] >= 2;
+}
+
+template <typename T, bool PG, bool SA>
+static int launch_stage_tma_i(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
+                              const void *pbase) {
+  typedef StageCfg<T, PG, SA, kTX, kTY, kNS> Cfg;
+  CUtensorMap tu, tp;
+  INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 3, &tu));
+  INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 4, &tp));
+  auto kern = k_stage3d_tma<T, PG, SA, kTX, kTY, kNS>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+    attr_set = true;
+  }
+  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
+  kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, a, g, visc, rh, volume<T>(c), zc, c->org[0], c->org[1], c->org[2]);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// ubase / pbase: START of the padded buffers (descriptors address the whole box); pbase == nullptr: no projection on load
+template <typename T>
+static int launch_stage_tma(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
+                            const void *pbase) {
+  const bool sa = a.sadd != nullptr;
+  if (pbase) return sa ? launch_stage_tma_i<T, true, true>(c, a, g, visc, rh, ubase, pbase)
+                       : launch_stage_tma_i<T, true, false>(c, a, g, visc, rh, ubase, pbase);
+  return sa ? launch_stage_tma_i<T, false, true>(c, a, g, visc, rh, ubase, c->preal)
+            : launch_stage_tma_i<T, false, false>(c, a, g, visc, rh, ubase, c->preal);
+}
+
+template <typename T, bool PG>
+static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh, const void *ubase, const void *pbase) {
+  typedef SmagCfg<T, PG, kTX, kTY, kNS> Cfg;
+  CUtensorMap tu, tp;
+  INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 4, &tu));
+  INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 5, &tp));
+  auto kern = k_smag3d_tma<T, PG, kTX, kTY, kNS>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+    attr_set = true;
+  }
+  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
+  kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc, c->org[0], c->org[1],
+                                          c->org[2]);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// s = smagorinsky_closure(u) into c->sbuf (interior) from the padded velocity buffer (ghosts valid, 2 layers)
+template <typename T>
+static int launch_smag_tma(insb200_ctx *c, double theta, const void *ubase, const void *pbase) {
+  ScopedTimer tm(c, TM_SMAGTENSOR);
+  Geo g = geo_compact(c);
+  T *sout = (T *)c->sbuf + c->corg;
+  if (pbase) return launch_smag_tma_i<T, true>(c, sout, g, eddy_const<T>(c, theta), make_rh<T>(c), ubase, pbase);
+  return launch_smag_tma_i<T, false>(c, sout, g, eddy_const<T>(c, theta), make_rh<T>(c), ubase, c->preal);
+}
+
 // fused momentum + stage combination, one thread per cell (any D, any n)
 template <typename T, int D>
 static int launch_stage(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, bool smag) {
@@ -905,7 +1055,85 @@ static int ensure_rk(insb200_ctx *c, const Tableau &tb, bool smag) {
   INS_TRY(ensure_fft(c));
   for (int b = 0; b < 3; b++) INS_TRY(ensure_vec(c, &c->ubuf[b]));
   for (int j = 0; j < tb.s; j++) if (tb.need[j]) INS_TRY(ensure_vec(c, &c->kbuf[j]));
-  if (smag) INS_TRY(ensure_sigma(c));
+  if (smag && !(c->D == 3 && c->padded && c->variant >= 2)) INS_TRY(ensure_sigma(c));
+  return 0;
+}
+
+// divergence(u') * Omega on plane 0 only (multi-rank TMA path: the chunk that starts at the slab's first
+// plane cannot recompute u'_z of the neighbour rank's last plane)
+template <typename T>
+static int launch_divergence_plane0(insb200_ctx *c, T *out, const T *u, Geo g) {
+  ScopedTimer tm(c, TM_DIVERGENCE);
+  dim3 blk(64, 4, 1), grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 3) / 4, 1);
+  k_divergence_planes<T><<<grd, blk, 0, c->stream>>>(out, u, c->csy, c->csz, c->ccomp, g, make_rh<T>(c), volume<T>(c), c->nloc[2]);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// one timestep! on the padded 3-D layout with the TMA kernels: per stage [closure kernel] + stage kernel
+// (k_i, u', Poisson right-hand side) + ghost refresh + cuFFT solve; the projection u = u' - grad p of
+// stages 1..s-1 is applied by the NEXT stage's plane pipeline, the last one by the gradient kernel.
+template <typename T>
+static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
+  const bool smag = !std::isnan(theta);
+  const Geo g = geo_compact(c);
+  const T visc = T(1) / T(c->Re);
+  const Rh<T> rh = make_rh<T>(c);
+  const i64 goff = c->corg;
+  const bool multi = c->nranks > 1;
+  if (smag) INS_TRY(ensure_vec(c, &c->sbuf));
+  INS_TRY(dev_alloc(c, &c->preal2, (size_t)c->ccomp * sizeof(T)));
+  INS_TRY((fill_ghosts<T>(c, c->ubuf[0], 3, 2, 2)));  // apply_bc_u! before momentum (:19)
+  int cur = 0;
+  bool pending = false;  // ubuf[cur] holds u' of the previous stage; its multiplier p is in preal2
+  for (int i = 0; i < tb.s; i++) {
+    const int nxt = (cur == 1) ? 2 : 1;
+    const bool last = i == tb.s - 1;
+    const void *pbase = nullptr;
+    if (pending) {
+      std::swap(c->preal, c->preal2);  // p of the previous stage -> preal2; preal receives the new right-hand side
+      pbase = c->preal2;
+    }
+    if (smag) INS_TRY((launch_smag_tma<T>(c, theta, c->ubuf[cur], pbase)));
+    StageArgs<T> a;
+    memset(&a, 0, sizeof a);
+    a.u = (const T *)c->ubuf[cur] + goff;
+    a.u0 = (const T *)c->ubuf[0] + goff;
+    a.u0_is_u = (cur == 0 && !pending) ? 1 : 0;
+    a.nk = 0;
+    for (int j = 0; j < i; j++) {
+      if (tb.A[i * tb.s + j] == 0.0) continue;  // exact: adds +-0
+      a.kin[a.nk] = (const T *)c->kbuf[j] + goff;
+      a.coef[a.nk] = T(dt) * T(tb.A[i * tb.s + j]);  // `dt * A[i,j]` formed first (:37)
+      a.nk++;
+    }
+    a.coef_self = T(dt) * T(tb.A[i * tb.s + i]);
+    a.kout = tb.need[i] ? (T *)c->kbuf[i] + goff : nullptr;
+    a.unew = (T *)c->ubuf[nxt] + goff;
+    a.force = c->force ? (const T *)c->force + goff : nullptr;
+    a.sadd = smag ? (const T *)c->sbuf + goff : nullptr;
+    a.div = (T *)c->preal + goff;
+    a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp; a.ssc = c->ccomp;
+    {
+      ScopedTimer tm(c, TM_STAGE);
+      INS_TRY((launch_stage_tma<T>(c, a, g, visc, rh, c->ubuf[cur], pbase)));
+    }
+    // apply_bc_u! (:48): ghosts of u' for the next stage's boxes (and, multi-rank, for the first plane's divergence)
+    if (!last) INS_TRY((fill_ghosts<T>(c, c->ubuf[nxt], 3, 2, 2)));
+    else if (multi) INS_TRY((halo_compact<T>(c, c->ubuf[nxt], 3, 1, 0)));
+    if (multi) INS_TRY((launch_divergence_plane0<T>(c, (T *)c->preal + goff, (const T *)c->ubuf[nxt] + goff, g)));
+    INS_TRY((poisson_solve<T, 3>(c)));
+    if (!last) {
+      INS_TRY((fill_ghosts<T>(c, c->preal, 1, 2, 3)));  // apply_bc_p! (pressure.jl:78)
+      pending = true;
+    } else {
+      INS_TRY((halo_compact<T>(c, c->preal, 1, 0, 1)));
+      INS_TRY((launch_gradient<T, 3, 1>(c, view_compact<T>(c, c->ubuf[nxt]), view_compact_c<T>(c, c->preal), g)));
+      pending = false;
+    }
+    cur = nxt;
+  }
+  std::swap(c->ubuf[0], c->ubuf[cur]);
   return 0;
 }
 
@@ -916,13 +1144,14 @@ static int ensure_rk(insb200_ctx *c, const Tableau &tb, bool smag) {
 // the last stage runs the gradient kernel.  Otherwise: stage kernel, divergence, solve, gradient.
 template <typename T, int D>
 static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
+  if (tma_supported<T, D>(c)) return rk_step_tma<T>(c, tb, dt, theta);
   const bool smag = !std::isnan(theta);
   const Geo g = geo_compact(c);
   const T visc = T(1) / T(c->Re);
   const Rh<T> rh = make_rh<T>(c);
   const bool tiled = tiled_stage_supported<T, D>(c);
   const bool fuse_grad = tiled && c->fuse_gradient;
-  const i64 goff = (i64)c->G * c->cplane;
+  const i64 goff = c->corg;
   T *pr = (T *)c->preal + goff;
   int cur = 0;
   bool pending = false;  // ubuf[cur] holds u' of the previous stage, its gradient correction is still in preal

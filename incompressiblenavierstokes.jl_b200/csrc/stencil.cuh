@@ -72,7 +72,9 @@ struct GradAcc {
 // ---------------------------------------------------------------------------------------------
 template <typename T, int D, bool CONV, bool DIFF, class A>
 __device__ __forceinline__ T convdiff_comp(const A &U, const int a, const T visc, const T (&rh)[3]) {
-  const T half = T(0.5);
+  // Algebra: (x/2)*(y/2+z/2) == ((x)*(y+z))/4 and (a/h - b/h) == (a-b)/h hold bit-for-bit when h is a
+  // power of two (scaling by 2^k commutes with rounding), so the forms below reproduce the reference's
+  // operation order exactly there with 16 instead of 22 flops per (a, b) pair.
   T f = T(0);
   const T uI = U(a, 0, 0, 0);
   const int ax = (a == 0), ay = (a == 1), az = (a == 2);
@@ -81,22 +83,16 @@ __device__ __forceinline__ T convdiff_comp(const A &U, const int a, const T visc
     const int bx = (b == 0), by = (b == 1), bz = (b == 2);
     const T um = U(a, -bx, -by, -bz);
     const T up = U(a, bx, by, bz);
-    T uu1 = T(0), uu2 = T(0), d1 = T(0), d2 = T(0);
+    T conv = T(0), diff = T(0);
     if (CONV) {
-      const T ua1 = (um + uI) * half;
-      const T ua2 = (uI + up) * half;
-      const T ub1 = half * U(b, -bx, -by, -bz) + half * U(b, ax - bx, ay - by, az - bz);
-      const T ub2 = half * U(b, 0, 0, 0) + half * U(b, ax, ay, az);
-      uu1 = ua1 * ub1;
-      uu2 = ua2 * ub2;
+      const T x1 = (um + uI) * (U(b, -bx, -by, -bz) + U(b, ax - bx, ay - by, az - bz));
+      const T x2 = (uI + up) * (U(b, 0, 0, 0) + U(b, ax, ay, az));
+      conv = (x2 - x1) * T(0.25);
     }
-    if (DIFF) {
-      d1 = (uI - um) * rh[b];
-      d2 = (up - uI) * rh[b];
-    }
-    if (CONV && DIFF) f += (visc * (d2 - d1) - (uu2 - uu1)) * rh[b];
-    else if (CONV) f -= (uu2 - uu1) * rh[b];
-    else f += visc * (d2 - d1) * rh[b];
+    if (DIFF) diff = ((up - uI) - (uI - um)) * rh[b];
+    if (CONV && DIFF) f += (visc * diff - conv) * rh[b];
+    else if (CONV) f -= conv * rh[b];
+    else f += visc * diff * rh[b];
   }
   return f;
 }
@@ -116,10 +112,10 @@ __device__ __forceinline__ T ddx(const A &U, const int a, const int b, const T (
   const int ax = (a == 0), ay = (a == 1), az = (a == 2);
   const int bx = (b == 0), by = (b == 1), bz = (b == 2);
   if (a == b) return (U(a, 0, 0, 0) - U(a, -bx, -by, -bz)) * rh[b];
-  return ((U(a, bx, by, bz) - U(a, 0, 0, 0)) * rh[b] +
-          (U(a, bx - ax, by - ay, bz - az) - U(a, -ax, -ay, -az)) * rh[b] +
-          (U(a, 0, 0, 0) - U(a, -bx, -by, -bz)) * rh[b] +
-          (U(a, -ax, -ay, -az) - U(a, -ax - bx, -ay - by, -az - bz)) * rh[b]) * T(0.25);
+  // ((A/h + B/h) + C/h + D/h)/4 == (((A+B)+C)+D) * (1/h * 0.25) bit-for-bit for power-of-two h
+  return ((((U(a, bx, by, bz) - U(a, 0, 0, 0)) + (U(a, bx - ax, by - ay, bz - az) - U(a, -ax, -ay, -az))) +
+           (U(a, 0, 0, 0) - U(a, -bx, -by, -bz))) +
+          (U(a, -ax, -ay, -az) - U(a, -ax - bx, -ay - by, -az - bz))) * (rh[b] * T(0.25));
 }
 
 // sig[symidx] at one p-cell; c_eddy = theta^2 * d^2 (formed on the host in T, left to right)
@@ -266,6 +262,8 @@ struct StageArgs {
   T *div;           // tiled kernels: nullable, receives divergence(unew) * Omega (the Poisson right-hand side)
   i64 sy, sz, sc;   // strides shared by all compact vector buffers
   i64 ssc;          // component stride of sigma
+  const T *sadd;    // TMA kernels: closure term s = div sigma added to k_i (nullable)
+  int u0_is_u;      // TMA kernels: ustart is the stage input itself (first stage): take it from the tile
 };
 
 template <typename T, int D, bool SMAG>

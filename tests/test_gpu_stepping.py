@@ -222,7 +222,10 @@ def test_kernel_variants_bit_identical(T, smag):
     for name, params in [("naive", dict(variant=0)),
                          ("tiled16", dict(variant=1, tile_y=16, zchunk=64, fuse_gradient=1)),
                          ("tiled8_zc16", dict(variant=1, tile_y=8, zchunk=16, fuse_gradient=1)),
-                         ("tiled16_zc7_nofuse", dict(variant=1, tile_y=16, zchunk=7, fuse_gradient=0))]:
+                         ("tiled16_zc7_nofuse", dict(variant=1, tile_y=16, zchunk=7, fuse_gradient=0)),
+                         ("tma_zc64", dict(variant=2, zchunk=64)),
+                         ("tma_zc7", dict(variant=2, zchunk=7)),
+                         ("tma_zc2", dict(variant=2, zchunk=2))]:
         for k, v in params.items():
             set_param(sc, k, v)
         u = ins.to_device(u0, sc)
