@@ -948,21 +948,23 @@ static int launch_divergence_planes(insb200_ctx *c, T *out, const T *u, Geo g) {
 }
 
 // ---- TMA plane-pipeline kernels (tma_stage.cuh): padded 3-D layout ---------------------------------
-static const int kTX = 32, kTY = 16, kNS = 4;
+static const int kTX = 32, kTY = 16;
 
 template <typename T, int D>
 static bool tma_supported(const insb200_ctx *c) {
-  return D == 3 && c->padded && c->variant >= 2 && c->nloc[0] % kTX == 0 && c->nloc[1] % kTY == 0 && c->nloc[2] >= 2;
+  // 32-bit element offsets inside the kernels: the three components of one buffer must stay below 2^31
+  return D == 3 && c->padded && c->variant >= 2 && c->nloc[0] % kTX == 0 && c->nloc[1] % kTY == 0 && c->nloc[2] >= 2 &&
+         3 * c->ccomp < ((i64)1 << 31);
 }
 
 template <typename T, bool PG, bool SA>
 static int launch_stage_tma_i(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
                               const void *pbase) {
-  typedef StageCfg<T, PG, SA, kTX, kTY, kNS> Cfg;
+  typedef StageCfg<T, PG, SA, kTX, kTY> Cfg;
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 3, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 4, &tp));
-  auto kern = k_stage3d_tma<T, PG, SA, kTX, kTY, kNS>;
+  auto kern = k_stage3d_tma<T, PG, SA, kTX, kTY>;
   static bool attr_set = false;
   if (!attr_set) {
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
@@ -988,11 +990,11 @@ static int launch_stage_tma(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc
 
 template <typename T, bool PG>
 static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh, const void *ubase, const void *pbase) {
-  typedef SmagCfg<T, PG, kTX, kTY, kNS> Cfg;
+  typedef SmagCfg<T, PG, kTX, kTY> Cfg;
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 4, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 5, &tp));
-  auto kern = k_smag3d_tma<T, PG, kTX, kTY, kNS>;
+  auto kern = k_smag3d_tma<T, PG, kTX, kTY>;
   static bool attr_set = false;
   if (!attr_set) {
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));

@@ -58,116 +58,113 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 // ---- plane pipeline -----------------------------------------------------------------------------
-// Slots hold planes q = 0, 1, 2, ... (q = z - zfirst).  With PGRAD the slot's barrier also covers the
-// pressure plane q+1 (and q for the very first request), which the in-place projection of plane q needs.
-template <typename T, int TX, int BYU, bool PGRAD, int NS>
+// NS = 4 velocity slots hold planes q-1, q, q+1 (consumed) and q+2 (landing); planes are numbered
+// q = 0, 1, 2, ... from the first plane of the block.  With PGRAD the slot's barrier also covers the
+// pressure plane q+1 (and q for the very first request), which the in-place projection of plane q needs;
+// NS+1 pressure slots because the prologue holds planes 0..NS at once.  All shared-memory addressing is
+// by element offset from one base pointer, and the slot offsets are rotated in registers (no modulo in
+// the plane loop).
+template <typename T, int TX, int BYU, bool PGRAD>
 struct PlanePipe {
+  static constexpr int NS = 4;
   static constexpr int V = 16 / (int)sizeof(T);   // elements per 16 B
   static constexpr int XL = V;                    // left x margin of the box (>= 2 halo cells)
   static constexpr int BX = TX + 2 * V;           // box width: i0-XL .. i0+TX+V-1
   static constexpr int BYP = BYU + 1;
-  static constexpr int NPS = NS + 1;              // pressure slots (the prologue holds planes 0 .. NS at once)
+  static constexpr int NPS = NS + 1;
   static constexpr int UPL = BYU * BX;            // elements of one component plane
   static constexpr int USLOT = ((3 * UPL * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
   static constexpr int PSLOT = ((BYP * BX * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
+  static constexpr int POFF = NS * USLOT;         // pressure slots follow the velocity slots
   static constexpr int ELEMS = NS * USLOT + (PGRAD ? NPS * PSLOT : 0);
   static constexpr uint32_t UBYTES = 3u * UPL * sizeof(T), PBYTES = (uint32_t)(BYP * BX * sizeof(T));
 
-  T *su, *sp;
-  uint64_t *full;
+  T *s;            // base of the slots
+  uint64_t *full;  // NS barriers
   const CUtensorMap *tmu, *tmp;
   int x0, y0, z0;  // tensor coordinates of the box origin of plane q = 0
 
   __device__ __forceinline__ void init(T *base, uint64_t *bars, const CUtensorMap *tu, const CUtensorMap *tp, int x0_,
                                        int y0_, int z0_, int tid) {
-    su = base;
-    sp = base + NS * USLOT;
+    s = base;
     full = bars;
     tmu = tu; tmp = tp;
     x0 = x0_; y0 = y0_; z0 = z0_;
     if (tid == 0) {
 #pragma unroll
-      for (int s = 0; s < NS; s++) mbar_init(&full[s], 1);
+      for (int i = 0; i < NS; i++) mbar_init(&full[i], 1);
       fence_barrier_init();
     }
   }
-  __device__ __forceinline__ T *uslot(int q) const { return su + (q % NS) * USLOT; }
-  __device__ __forceinline__ T *pslot(int q) const { return sp + (q % NPS) * PSLOT; }
+  static __device__ __forceinline__ int uoff(int q) { return (q & (NS - 1)) * USLOT; }
+  static __device__ __forceinline__ int poff(int q) { return POFF + (q % NPS) * PSLOT; }
 
   // one thread: request plane q (all three velocity components; the pressure planes it needs)
   __device__ __forceinline__ void issue(int q) const {
-    uint64_t *bar = &full[q % NS];
+    uint64_t *bar = &full[q & (NS - 1)];
     fence_proxy_async();  // earlier generic-proxy accesses of the slot are ordered before the bulk write
     if (PGRAD) {
       mbar_expect_tx(bar, UBYTES + (q == 0 ? 2u : 1u) * PBYTES);
-      if (q == 0) tma_load_4d(pslot(0), tmp, bar, x0, y0, z0, 0);
-      tma_load_4d(pslot(q + 1), tmp, bar, x0, y0, z0 + q + 1, 0);
+      if (q == 0) tma_load_4d(s + poff(0), tmp, bar, x0, y0, z0, 0);
+      tma_load_4d(s + poff(q + 1), tmp, bar, x0, y0, z0 + q + 1, 0);
     } else {
       mbar_expect_tx(bar, UBYTES);
     }
-    tma_load_4d(uslot(q), tmu, bar, x0, y0, z0 + q, 0);
+    tma_load_4d(s + uoff(q), tmu, bar, x0, y0, z0 + q, 0);
   }
-  __device__ __forceinline__ void wait(int q) const { mbar_wait(&full[q % NS], (uint32_t)((q / NS) & 1)); }
+  __device__ __forceinline__ void wait(int q) const { mbar_wait(&full[q & (NS - 1)], (uint32_t)((q >> 2) & 1)); }
 
   // all threads: u(q) = u'(q) - grad p over the whole box (the last column / row of the box is never
-  // consumed, so the neighbour reads p[l+1], p[l+BX] may run into the next row / the extra p row)
-  __device__ __forceinline__ void project(int q, int tid, int nt, const T (&rh)[3]) const {
+  // consumed, so the neighbour reads p[l+1], p[l+BX] may run into the next row / the extra p row).
+  // uo = velocity slot offset, po / pn = slot offsets of pressure planes q and q+1.
+  __device__ __forceinline__ void project(int uo, int po, int pn, int tid, int nt, const T (&rh)[3]) const {
     if (!PGRAD) return;
-    T *u = uslot(q);
-    const T *p = pslot(q), *pn = pslot(q + 1);
+    T *u = s + uo;
+    const T *p = s + po, *p1 = s + pn;
     for (int l = tid; l < UPL; l += nt) {
       const T p0 = p[l];
       u[l] = u[l] - (p[l + 1] - p0) * rh[0];
       u[UPL + l] = u[UPL + l] - (p[l + BX] - p0) * rh[1];
-      u[2 * UPL + l] = u[2 * UPL + l] - (pn[l] - p0) * rh[2];
+      u[2 * UPL + l] = u[2 * UPL + l] - (p1[l] - p0) * rh[2];
     }
   }
-};
-
-// velocity accessor on three resident plane slots
-template <typename T, int BX, int UPL>
-struct PlaneAcc {
-  const T *pm, *p0, *pp;  // planes k-1, k, k+1
-  int c0;                 // offset of the cell inside a component plane
-  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
-    const T *b = dz < 0 ? pm : (dz > 0 ? pp : p0);
-    return b[c * UPL + c0 + dy * BX + dx];
+  __device__ __forceinline__ void project_q(int q, int tid, int nt, const T (&rh)[3]) const {
+    project(uoff(q), poff(q), poff(q + 1), tid, nt, rh);
   }
 };
 
-// one component `a` of the stage at a cell: f = momentum!(u)[a] (+ force + s), return u' (the combination).
-//   og = global element offset of the cell in the padded buffers (without the component stride)
-template <typename T, bool SADD, class ACC>
-__device__ __forceinline__ T stage_comp_p(const StageArgs<T> &A, const ACC &U, const int a, const i64 og, const T visc,
-                                          const T (&rh)[3], T &f_out) {
-  T f = convdiff_comp<T, 3, true, true>(U, a, visc, rh);
-  const i64 o = og + a * A.sc;
-  if (A.force) f = f + __ldg(A.force + o);
-  if (SADD) f = f + __ldg(A.sadd + o);
-  f_out = f;
-  T acc = A.u0_is_u ? U(a, 0, 0, 0) : __ldg(A.u0 + o);
-  for (int q = 0; q < A.nk; q++) acc = acc + A.coef[q] * __ldg(A.kin[q] + o);
-  return acc + A.coef_self * f;
-}
-
-template <typename T, bool PGRAD, bool SADD, int TX, int TY, int NS>
-struct StageCfg {
-  typedef PlanePipe<T, TX, TY + 3, PGRAD, NS> Pipe;
-  static constexpr int NT = TX * TY;
-  static constexpr size_t SMEM = 128 + (size_t)Pipe::ELEMS * sizeof(T) + (size_t)(2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T) + 8 * NS + 16;
+// velocity accessor on three resident plane slots: element offsets (slot + own cell) from one base
+template <typename T, int BX, int UPL>
+struct PlaneAcc {
+  const T *s;
+  int om, o0, op;  // planes k-1, k, k+1
+  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
+    const int o = dz < 0 ? om : (dz > 0 ? op : o0);
+    return s[o + c * UPL + dy * BX + dx];
+  }
 };
 
-template <typename T, bool PGRAD, bool SADD, int TX, int TY, int NS>
+template <typename T, bool PGRAD, bool SADD, int TX, int TY>
+struct StageCfg {
+  typedef PlanePipe<T, TX, TY + 3, PGRAD> Pipe;
+  static constexpr int NT = TX * TY;
+  static constexpr size_t SMEM = 128 + (size_t)Pipe::ELEMS * sizeof(T) + (size_t)(2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T) + 8 * Pipe::NS + 16;
+};
+
+// Global addressing inside the kernel uses 32-bit element offsets (the host checks 3*ccomp < 2^31):
+// one IMAD.WIDE per access instead of a 64-bit add chain.
+template <typename T, bool PGRAD, bool SADD, int TX, int TY>
 __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
     k_stage3d_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p, StageArgs<T> A, Geo g,
                   T visc, Rh<T> rh, T vol, int zc, int ox, int oy, int oz) {
-  typedef StageCfg<T, PGRAD, SADD, TX, TY, NS> Cfg;
+  typedef StageCfg<T, PGRAD, SADD, TX, TY> Cfg;
   typedef typename Cfg::Pipe Pipe;
-  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL;
+  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL, NS = Pipe::NS;
+  constexpr int POFF = Pipe::POFF, PSLOT = Pipe::PSLOT, PEND = POFF + Pipe::NPS * PSLOT;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *sb = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
-  T *sbase = reinterpret_cast<T *>(sb);
-  T *sdx = sbase + Pipe::ELEMS;                       // [2][TY][TX+1]  u'_x incl. column -1
+  T *su = reinterpret_cast<T *>(sb);
+  T *sdx = su + Pipe::ELEMS;                          // [2][TY][TX+1]  u'_x incl. column -1
   T *sdy = sdx + 2 * TY * (TX + 1);                   // [2][TY+1][TX]  u'_y incl. row -1
   uint64_t *bars = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(sdy + 2 * (TY + 1) * TX) + 7) & ~(uintptr_t)7);
 
@@ -175,11 +172,20 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
   const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
   const int kbeg = blockIdx.z * zc, kend = min(kbeg + zc, g.n[2]);
   const int n0 = g.n[0], n1 = g.n[1], n2 = g.n[2];
-  const i64 sy = A.sy, sz = A.sz;
+  const unsigned sy = (unsigned)A.sy, sz = (unsigned)A.sz, sc = (unsigned)A.sc;
+  const T *__restrict__ pu0 = A.u0;
+  const T *__restrict__ pforce = A.force;
+  const T *__restrict__ psadd = A.sadd;
+  T *__restrict__ pkout = A.kout;
+  T *__restrict__ punew = A.unew;
+  T *__restrict__ pdiv = A.div;
+  const bool has_force = pforce != nullptr, has_kout = pkout != nullptr, u0_tile = A.u0_is_u != 0;
+  const int nk = A.nk;
+  const T coef_self = A.coef_self;
 
   // plane q <-> z = kbeg - 2 + q
   Pipe pipe;
-  pipe.init(sbase, bars, &tm_u, &tm_p, ox + i0 - XL, oy + j0 - 2, oz + kbeg - 2, tid);
+  pipe.init(su, bars, &tm_u, &tm_p, ox + i0 - XL, oy + j0 - 2, oz + kbeg - 2, tid);
   __syncthreads();
   const int qlast = kend - kbeg + 2;  // plane kend
   if (tid == 0) {
@@ -191,74 +197,121 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
 #pragma unroll
   for (int q = 0; q < 4; q++) {
     pipe.wait(q);
-    pipe.project(q, tid, NT, rh.v);
+    pipe.project_q(q, tid, NT, rh.v);
   }
   __syncthreads();
 
   const int gi = i0 + tx, gj = j0 + ty;
-  const i64 ocell = (i64)gj * sy + gi;
+  const unsigned ocell = (unsigned)gj * sy + gi;
   // the extra point of some threads on the minus halo: warp 1 (first TY lanes): (-1, l) component x;
-  // warp 2: (l, -1) component y  (different warps / schedulers than each other)
+  // warp 2: (l, -1) component y  (two different warps on two different schedulers)
   const bool hx = tid >= 32 && tid < 32 + TY, hy = tid >= 64 && tid < 64 + TX;
+  const bool hany = hx || hy;
   const int hlx = hx ? -1 : tid - 64, hly = hx ? tid - 32 : -1;
   const int hgi = wrapi(i0 + hlx, n0, 1), hgj = wrapi(j0 + hly, n1, 1);
-  const i64 ohalo = (i64)hgj * sy + hgi;
+  const unsigned ohalo = (unsigned)hgj * sy + hgi + (hx ? 0u : sc);  // component offset included
+  const int ha = hx ? 0 : 1;
   const int c_own = (ty + 2) * BX + tx + XL;
-  const int c_halo = (hly + 2) * BX + hlx + XL;
+  const int c_halo = hany ? (hly + 2) * BX + hlx + XL : c_own;
+
+  // f (convection-diffusion) -> k_i and u' of one component at one cell; o = global offset incl. component
+  auto combine = [&](T f, const unsigned o, const T uc, const T l_u0, const T l_s, const T l_f, T &f_out) -> T {
+    if (has_force) f = f + l_f;
+    if (SADD) f = f + l_s;
+    f_out = f;
+    T acc = u0_tile ? uc : l_u0;
+    for (int q = 0; q < nk; q++) acc = acc + A.coef[q] * __ldg(A.kin[q] + o);
+    return acc + coef_self * f;
+  };
 
   // u'_z of plane kbeg-1 (for the z-difference of the divergence on the first plane of the chunk)
   T uz_prev = T(0);
   const bool have_prev = kbeg > 0 || g.wrap[2];  // otherwise plane 0 is completed by k_divergence_planes
-  if (A.div && have_prev) {
+  if (pdiv && have_prev) {
     const int kz = wrapi(kbeg - 1, n2, g.wrap[2]);
-    PlaneAcc<T, BX, UPL> U{pipe.uslot(0), pipe.uslot(1), pipe.uslot(2), c_own};
+    const unsigned o = (unsigned)kz * sz + ocell + 2u * sc;
+    PlaneAcc<T, BX, UPL> U{su, Pipe::uoff(0) + c_own, Pipe::uoff(1) + c_own, Pipe::uoff(2) + c_own};
+    const T l_u0 = u0_tile ? T(0) : __ldg(pu0 + o);
+    const T l_s = SADD ? __ldg(psadd + o) : T(0);
+    const T l_f = has_force ? __ldg(pforce + o) : T(0);
     T f;
-    uz_prev = stage_comp_p<T, SADD>(A, U, 2, (i64)kz * sz + ocell, visc, rh.v, f);
+    uz_prev = combine(convdiff_comp<T, 3, true, true>(U, 2, visc, rh.v), o, U(2, 0, 0, 0), l_u0, l_s, l_f, f);
   }
   __syncthreads();  // plane 0 is retired: its slot takes plane NS
   if (tid == 0 && NS <= qlast) pipe.issue(NS);
 
+  int s_m = Pipe::uoff(1), s_0 = Pipe::uoff(2), s_p = Pipe::uoff(3), s_n = Pipe::uoff(0);  // planes q-1, q, q+1, q+2 at q = 2
+  int pa = Pipe::poff(4), pb = Pipe::poff(5);                                             // pressure planes q+2, q+3
+  unsigned o = (unsigned)kbeg * sz + ocell, oh = (unsigned)kbeg * sz + ohalo;
+  // global operands (ustart, closure term, force) are software-pipelined one plane ahead in registers:
+  // requested as one batch before the barrier of iteration k-1, consumed at the end of iteration k
+  T n_u0[3], n_s[3], n_f[3], nh_u0 = T(0), nh_s = T(0), nh_f = T(0);
+  auto fetch_operands = [&](const unsigned oo, const unsigned ooh) {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      n_u0[a] = u0_tile ? T(0) : __ldg(pu0 + oo + a * sc);
+      n_s[a] = SADD ? __ldg(psadd + oo + a * sc) : T(0);
+      n_f[a] = has_force ? __ldg(pforce + oo + a * sc) : T(0);
+    }
+    if (pdiv && hany) {
+      if (!u0_tile) nh_u0 = __ldg(pu0 + ooh);
+      if (SADD) nh_s = __ldg(psadd + ooh);
+      if (has_force) nh_f = __ldg(pforce + ooh);
+    }
+  };
+  fetch_operands(o, oh);
   for (int k = kbeg; k < kend; k++) {
     const int q = k - kbeg + 2;  // plane number of k
-    PlaneAcc<T, BX, UPL> U{pipe.uslot(q - 1), pipe.uslot(q), pipe.uslot(q + 1), c_own};
-    const i64 ozk = (i64)k * sz;
+    T l_u0[3], l_s[3], l_f[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) { l_u0[a] = n_u0[a]; l_s[a] = n_s[a]; l_f[a] = n_f[a]; }
+    const T h_u0 = nh_u0, h_s = nh_s, h_f = nh_f;
+    PlaneAcc<T, BX, UPL> U{su, s_m + c_own, s_0 + c_own, s_p + c_own};
     T un[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) {
       T f;
-      un[a] = stage_comp_p<T, SADD>(A, U, a, ozk + ocell, visc, rh.v, f);
-      const i64 og = ozk + ocell + a * A.sc;
-      if (A.kout) A.kout[og] = f;
-      A.unew[og] = un[a];
+      un[a] = combine(convdiff_comp<T, 3, true, true>(U, a, visc, rh.v), o + a * sc, U(a, 0, 0, 0), l_u0[a], l_s[a], l_f[a], f);
+      if (has_kout) pkout[o + a * sc] = f;
+      punew[o + a * sc] = un[a];
     }
-    if (A.div) {
+    if (pdiv) {
       T *bx = sdx + (k & 1) * TY * (TX + 1), *by = sdy + (k & 1) * (TY + 1) * TX;
       bx[ty * (TX + 1) + tx + 1] = un[0];
       by[(ty + 1) * TX + tx] = un[1];
-      if (hx || hy) {
-        PlaneAcc<T, BX, UPL> Uh{pipe.uslot(q - 1), pipe.uslot(q), pipe.uslot(q + 1), c_halo};
+      if (hany) {
+        PlaneAcc<T, BX, UPL> Uh{su, s_m + c_halo, s_0 + c_halo, s_p + c_halo};
         T f;
-        if (hx) bx[hly * (TX + 1)] = stage_comp_p<T, SADD>(A, Uh, 0, ozk + ohalo, visc, rh.v, f);
-        else by[hlx] = stage_comp_p<T, SADD>(A, Uh, 1, ozk + ohalo, visc, rh.v, f);
+        const T fc = hx ? convdiff_comp<T, 3, true, true>(Uh, 0, visc, rh.v) : convdiff_comp<T, 3, true, true>(Uh, 1, visc, rh.v);
+        const T v = combine(fc, oh, Uh(ha, 0, 0, 0), h_u0, h_s, h_f, f);
+        if (hx) bx[hly * (TX + 1)] = v;
+        else by[hlx] = v;
       }
     }
     // plane k+2 for the next iteration
     if (k + 1 < kend) {
+      fetch_operands(o + sz, oh + sz);
       pipe.wait(q + 2);
-      pipe.project(q + 2, tid, NT, rh.v);
+      pipe.project(s_n, pa, pb, tid, NT, rh.v);
     }
     __syncthreads();
-    // slot of plane k-1 is free now: request plane k+NS-1
-    if (tid == 0 && q - 1 + NS <= qlast) pipe.issue(q - 1 + NS);
-    if (A.div && (k > kbeg || have_prev)) {
+    // slot of plane k-1 is free now: request plane k+3
+    if (tid == 0 && q + 3 <= qlast) pipe.issue(q + 3);
+    if (pdiv && (k > kbeg || have_prev)) {
       const T *bx = sdx + (k & 1) * TY * (TX + 1), *by = sdy + (k & 1) * (TY + 1) * TX;
       T d = T(0);
       d += (un[0] - bx[ty * (TX + 1) + tx]) * rh.v[0];
       d += (un[1] - by[ty * TX + tx]) * rh.v[1];
       d += (un[2] - uz_prev) * rh.v[2];
-      A.div[ozk + ocell] = d * vol;
+      pdiv[o] = d * vol;
     }
     uz_prev = un[2];
+    const int t = s_m;
+    s_m = s_0; s_0 = s_p; s_p = s_n; s_n = t;
+    pa = pb;
+    pb = pb + PSLOT == PEND ? POFF : pb + PSLOT;
+    o += sz;
+    oh += sz;
   }
 }
 
@@ -270,42 +323,44 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
 // -------------------------------------------------------------------------------------------------
 template <typename T, int SX, int SPL>
 struct SigmaAcc {
-  const T *sm, *s0, *sp;  // sigma planes k-1, k, k+1
-  int c0;
+  const T *s;
+  int om, o0, op;  // sigma planes k-1, k, k+1 (slot + own cell)
   __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
-    const T *b = dz < 0 ? sm : (dz > 0 ? sp : s0);
-    return b[c * SPL + c0 + dy * SX + dx];
+    const int o = dz < 0 ? om : (dz > 0 ? op : o0);
+    return s[o + c * SPL + dy * SX + dx];
   }
 };
 
-template <typename T, bool PGRAD, int TX, int TY, int NS>
+template <typename T, bool PGRAD, int TX, int TY>
 struct SmagCfg {
-  typedef PlanePipe<T, TX, TY + 4, PGRAD, NS> Pipe;
+  typedef PlanePipe<T, TX, TY + 4, PGRAD> Pipe;
   static constexpr int NT = TX * TY;
   static constexpr int SX = TX + 2, SY = TY + 2, SPL = SX * SY, SSLOT = 6 * SPL;
-  static constexpr size_t SMEM = 128 + (size_t)(Pipe::ELEMS + 3 * SSLOT) * sizeof(T) + 8 * NS + 16;
+  static constexpr size_t SMEM = 128 + (size_t)(Pipe::ELEMS + 3 * SSLOT) * sizeof(T) + 8 * Pipe::NS + 16;
 };
 
-template <typename T, bool PGRAD, int TX, int TY, int NS>
+template <typename T, bool PGRAD, int TX, int TY>
 __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
     k_smag3d_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p, T *__restrict__ sout,
-                 i64 sy, i64 sz, i64 sc, Geo g, T c_eddy, Rh<T> rh, int zc, int ox, int oy, int oz) {
-  typedef SmagCfg<T, PGRAD, TX, TY, NS> Cfg;
+                 i64 sy_, i64 sz_, i64 sc_, Geo g, T c_eddy, Rh<T> rh, int zc, int ox, int oy, int oz) {
+  typedef SmagCfg<T, PGRAD, TX, TY> Cfg;
   typedef typename Cfg::Pipe Pipe;
-  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL;
+  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL, NS = Pipe::NS;
+  constexpr int POFF = Pipe::POFF, PSLOT = Pipe::PSLOT, PEND = POFF + Pipe::NPS * PSLOT;
   constexpr int SX = Cfg::SX, SPL = Cfg::SPL, SSLOT = Cfg::SSLOT;
+  constexpr int SOFF = Pipe::ELEMS;  // sigma ring follows the plane slots
   extern __shared__ unsigned char smem_raw[];
   unsigned char *sb = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
-  T *sbase = reinterpret_cast<T *>(sb);
-  T *ssig = sbase + Pipe::ELEMS;  // [3][6][SY][SX]
-  uint64_t *bars = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(ssig + 3 * SSLOT) + 7) & ~(uintptr_t)7);
+  T *su = reinterpret_cast<T *>(sb);
+  uint64_t *bars = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(su + SOFF + 3 * SSLOT) + 7) & ~(uintptr_t)7);
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
   const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
   const int kbeg = blockIdx.z * zc, kend = min(kbeg + zc, g.n[2]);
+  const unsigned sy = (unsigned)sy_, sz = (unsigned)sz_, sc = (unsigned)sc_;
 
   Pipe pipe;
-  pipe.init(sbase, bars, &tm_u, &tm_p, ox + i0 - XL, oy + j0 - 2, oz + kbeg - 2, tid);
+  pipe.init(su, bars, &tm_u, &tm_p, ox + i0 - XL, oy + j0 - 2, oz + kbeg - 2, tid);
   __syncthreads();
   const int qlast = kend - kbeg + 3;  // velocity plane z = kend+1
   if (tid == 0) {
@@ -316,46 +371,66 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
 #pragma unroll
   for (int q = 0; q < 4; q++) {
     pipe.wait(q);
-    pipe.project(q, tid, NT, rh.v);
+    pipe.project_q(q, tid, NT, rh.v);
   }
   __syncthreads();
 
-  // sigma plane r from velocity planes r, r+1, r+2 over the (TX+2) x (TY+2) p-cells of the tile
-  auto sigma_plane = [&](int r) {
-    T *dst = ssig + (r % 3) * SSLOT;
-    for (int l = tid; l < SPL; l += NT) {
-      const int ly = l / SX, lx = l - ly * SX;  // p-cell (lx-1, ly-1) of the tile
-      PlaneAcc<T, BX, UPL> U{pipe.uslot(r), pipe.uslot(r + 1), pipe.uslot(r + 2), (ly + 1) * BX + lx - 1 + XL};
-      T sig[6];
+  // the (up to two) p-cells of this thread in the (TX+2) x (TY+2) sigma tile: l = tid and l = tid + NT
+  const int l0 = tid, l1 = tid + NT;
+  const int l0y = l0 / SX, l0x = l0 - l0y * SX;
+  const int l1y = l1 / SX, l1x = l1 - l1y * SX;
+  const int cu0 = (l0y + 1) * BX + l0x - 1 + XL, cu1 = (l1y + 1) * BX + l1x - 1 + XL;  // p-cell (lx-1, ly-1)
+  const bool two = l1 < SPL;
+  // sigma plane into ring slot offset `so` from velocity slots um, u0, up
+  auto sigma_plane = [&](int so, int um, int u0, int up) {
+    T sig[6];
+    {
+      PlaneAcc<T, BX, UPL> U{su, um + cu0, u0 + cu0, up + cu0};
       smag_sigma<T, 3>(U, c_eddy, rh.v, sig);
 #pragma unroll
-      for (int c = 0; c < 6; c++) dst[c * SPL + l] = sig[c];
+      for (int c = 0; c < 6; c++) su[so + c * SPL + l0] = sig[c];
+    }
+    if (two) {
+      PlaneAcc<T, BX, UPL> U{su, um + cu1, u0 + cu1, up + cu1};
+      smag_sigma<T, 3>(U, c_eddy, rh.v, sig);
+#pragma unroll
+      for (int c = 0; c < 6; c++) su[so + c * SPL + l1] = sig[c];
     }
   };
-  sigma_plane(0);
-  sigma_plane(1);
+  sigma_plane(SOFF, Pipe::uoff(0), Pipe::uoff(1), Pipe::uoff(2));
+  sigma_plane(SOFF + SSLOT, Pipe::uoff(1), Pipe::uoff(2), Pipe::uoff(3));
   __syncthreads();  // velocity planes 0 and 1 are retired
   if (tid == 0) {
     if (NS <= qlast) pipe.issue(NS);
     if (NS + 1 <= qlast) pipe.issue(NS + 1);
   }
 
-  const i64 ocell = (i64)(j0 + ty) * sy + i0 + tx;
   const int c_sig = (ty + 1) * SX + tx + 1;
+  // at r = 1: velocity planes r+1, r+2 resident (slots 2, 3), r+3 landing in slot 0, r+4 in slot 1
+  int u_a = Pipe::uoff(2), u_b = Pipe::uoff(3), u_c = Pipe::uoff(0), u_d = Pipe::uoff(1);
+  int pa = Pipe::poff(4), pb = Pipe::poff(5);          // pressure planes r+3, r+4
+  int g_m = SOFF, g_0 = SOFF + SSLOT, g_p = SOFF + 2 * SSLOT;  // sigma planes r-1, r, r+1
+  unsigned o = (unsigned)kbeg * sz + (unsigned)(j0 + ty) * sy + i0 + tx;
   for (int k = kbeg; k < kend; k++) {
     const int r = k - kbeg + 1;  // sigma plane number of k
     // sigma(k+1) needs velocity planes r+1, r+2, r+3 (z = k .. k+2)
     pipe.wait(r + 3);
-    pipe.project(r + 3, tid, NT, rh.v);
+    pipe.project(u_c, pa, pb, tid, NT, rh.v);
     __syncthreads();
-    sigma_plane(r + 1);
+    sigma_plane(g_p, u_a, u_b, u_c);
     __syncthreads();
     // velocity plane r+1 (z = k) is retired: its slot takes plane r+1+NS
     if (tid == 0 && r + 1 + NS <= qlast) pipe.issue(r + 1 + NS);
-    SigmaAcc<T, SX, SPL> Sg{ssig + ((r - 1) % 3) * SSLOT, ssig + (r % 3) * SSLOT, ssig + ((r + 1) % 3) * SSLOT, c_sig};
-    const i64 og = (i64)k * sz + ocell;
+    SigmaAcc<T, SX, SPL> Sg{su, g_m + c_sig, g_0 + c_sig, g_p + c_sig};
 #pragma unroll
-    for (int a = 0; a < 3; a++) sout[og + a * sc] = divsigma_comp<T, 3>(Sg, a, rh.v);
+    for (int a = 0; a < 3; a++) sout[o + a * sc] = divsigma_comp<T, 3>(Sg, a, rh.v);
+    const int t = u_a;
+    u_a = u_b; u_b = u_c; u_c = u_d; u_d = t;
+    const int gt = g_m;
+    g_m = g_0; g_0 = g_p; g_p = gt;
+    pa = pb;
+    pb = pb + PSLOT == PEND ? POFF : pb + PSLOT;
+    o += sz;
   }
 }
 
