@@ -957,14 +957,16 @@ static bool tma_supported(const insb200_ctx *c) {
          3 * c->ccomp < ((i64)1 << 31);
 }
 
-template <typename T, bool PG, bool SA>
-static int launch_stage_tma_i(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
+static const int kNS = 5;  // velocity plane slots of the stage kernel (prefetch distance 2 planes)
+
+template <typename T, bool PG, bool SA, bool GEN>
+static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
                               const void *pbase) {
-  typedef StageCfg<T, PG, SA, kTX, kTY> Cfg;
+  typedef StageCfg<T, PG, kTX, kTY, kNS> Cfg;
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 3, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 4, &tp));
-  auto kern = k_stage3d_tma<T, PG, SA, kTX, kTY>;
+  auto kern = k_stage3d_tma<T, PG, SA, GEN, kTX, kTY, kNS>;
   static bool attr_set = false;
   if (!attr_set) {
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
@@ -977,15 +979,17 @@ static int launch_stage_tma_i(insb200_ctx *c, const StageArgs<T> &a, Geo g, T vi
   return 0;
 }
 
-// ubase / pbase: START of the padded buffers (descriptors address the whole box); pbase == nullptr: no projection on load
+// ubase / pbase: START of the padded buffers (descriptors address the whole box); pbase == nullptr: first
+// stage (no projection on load, ustart is the stage input itself)
 template <typename T>
-static int launch_stage_tma(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
+static int launch_stage_tma(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
                             const void *pbase) {
-  const bool sa = a.sadd != nullptr;
-  if (pbase) return sa ? launch_stage_tma_i<T, true, true>(c, a, g, visc, rh, ubase, pbase)
-                       : launch_stage_tma_i<T, true, false>(c, a, g, visc, rh, ubase, pbase);
-  return sa ? launch_stage_tma_i<T, false, true>(c, a, g, visc, rh, ubase, c->preal)
-            : launch_stage_tma_i<T, false, false>(c, a, g, visc, rh, ubase, c->preal);
+  const bool sa = a.sadd[0] != nullptr, gen = a.nk > 0 || a.kout[0] == nullptr;
+  const void *pb = pbase ? pbase : c->preal;
+#define LST(PG, SA, GEN) launch_stage_tma_i<T, PG, SA, GEN>(c, a, g, visc, rh, ubase, pb)
+  if (pbase) return sa ? (gen ? LST(true, true, true) : LST(true, true, false)) : (gen ? LST(true, false, true) : LST(true, false, false));
+  return sa ? (gen ? LST(false, true, true) : LST(false, true, false)) : (gen ? LST(false, false, true) : LST(false, false, false));
+#undef LST
 }
 
 template <typename T, bool PG>
@@ -1097,11 +1101,17 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
       pbase = c->preal2;
     }
     if (smag) INS_TRY((launch_smag_tma<T>(c, theta, c->ubuf[cur], pbase)));
-    StageArgs<T> a;
+    TmaStageArgs<T> a;
     memset(&a, 0, sizeof a);
-    a.u = (const T *)c->ubuf[cur] + goff;
-    a.u0 = (const T *)c->ubuf[0] + goff;
-    a.u0_is_u = (cur == 0 && !pending) ? 1 : 0;
+    for (int q = 0; q < 3; q++) {
+      const i64 co = goff + q * c->ccomp;
+      a.u0[q] = (const T *)c->ubuf[0] + co;
+      a.sadd[q] = smag ? (const T *)c->sbuf + co : nullptr;
+      a.force[q] = c->force ? (const T *)c->force + co : nullptr;
+      a.kout[q] = tb.need[i] ? (T *)c->kbuf[i] + co : nullptr;
+      a.unew[q] = (T *)c->ubuf[nxt] + co;
+    }
+    a.div = (T *)c->preal + goff;
     a.nk = 0;
     for (int j = 0; j < i; j++) {
       if (tb.A[i * tb.s + j] == 0.0) continue;  // exact: adds +-0
@@ -1110,12 +1120,7 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
       a.nk++;
     }
     a.coef_self = T(dt) * T(tb.A[i * tb.s + i]);
-    a.kout = tb.need[i] ? (T *)c->kbuf[i] + goff : nullptr;
-    a.unew = (T *)c->ubuf[nxt] + goff;
-    a.force = c->force ? (const T *)c->force + goff : nullptr;
-    a.sadd = smag ? (const T *)c->sbuf + goff : nullptr;
-    a.div = (T *)c->preal + goff;
-    a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp; a.ssc = c->ccomp;
+    a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp;
     {
       ScopedTimer tm(c, TM_STAGE);
       INS_TRY((launch_stage_tma<T>(c, a, g, visc, rh, c->ubuf[cur], pbase)));

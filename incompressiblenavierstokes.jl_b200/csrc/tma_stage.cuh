@@ -58,15 +58,15 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
 
 // ---- plane pipeline -----------------------------------------------------------------------------
-// NS = 4 velocity slots hold planes q-1, q, q+1 (consumed) and q+2 (landing); planes are numbered
+// NS velocity slots hold planes q-1, q, q+1 (consumed), q+2 (landing) [and q+3 in flight, NS = 5]; planes are numbered
 // q = 0, 1, 2, ... from the first plane of the block.  With PGRAD the slot's barrier also covers the
 // pressure plane q+1 (and q for the very first request), which the in-place projection of plane q needs;
 // NS+1 pressure slots because the prologue holds planes 0..NS at once.  All shared-memory addressing is
 // by element offset from one base pointer, and the slot offsets are rotated in registers (no modulo in
 // the plane loop).
-template <typename T, int TX, int BYU, bool PGRAD>
+template <typename T, int TX, int BYU, bool PGRAD, int NS_>
 struct PlanePipe {
-  static constexpr int NS = 4;
+  static constexpr int NS = NS_;
   static constexpr int V = 16 / (int)sizeof(T);   // elements per 16 B
   static constexpr int XL = V;                    // left x margin of the box (>= 2 halo cells)
   static constexpr int BX = TX + 2 * V;           // box width: i0-XL .. i0+TX+V-1
@@ -96,12 +96,12 @@ struct PlanePipe {
       fence_barrier_init();
     }
   }
-  static __device__ __forceinline__ int uoff(int q) { return (q & (NS - 1)) * USLOT; }
+  static __device__ __forceinline__ int uoff(int q) { return (q % NS) * USLOT; }
   static __device__ __forceinline__ int poff(int q) { return POFF + (q % NPS) * PSLOT; }
 
   // one thread: request plane q (all three velocity components; the pressure planes it needs)
   __device__ __forceinline__ void issue(int q) const {
-    uint64_t *bar = &full[q & (NS - 1)];
+    uint64_t *bar = &full[q % NS];
     fence_proxy_async();  // earlier generic-proxy accesses of the slot are ordered before the bulk write
     if (PGRAD) {
       mbar_expect_tx(bar, UBYTES + (q == 0 ? 2u : 1u) * PBYTES);
@@ -112,7 +112,8 @@ struct PlanePipe {
     }
     tma_load_4d(s + uoff(q), tmu, bar, x0, y0, z0 + q, 0);
   }
-  __device__ __forceinline__ void wait(int q) const { mbar_wait(&full[q & (NS - 1)], (uint32_t)((q >> 2) & 1)); }
+  __device__ __forceinline__ void wait(int q) const { mbar_wait(&full[q % NS], (uint32_t)((q / NS) & 1)); }
+  __device__ __forceinline__ void wait_slot(int slot, uint32_t parity) const { mbar_wait(&full[slot], parity); }
 
   // all threads: u(q) = u'(q) - grad p over the whole box (the last column / row of the box is never
   // consumed, so the neighbour reads p[l+1], p[l+BX] may run into the next row / the extra p row).
@@ -144,23 +145,53 @@ struct PlaneAcc {
   }
 };
 
-template <typename T, bool PGRAD, bool SADD, int TX, int TY>
-struct StageCfg {
-  typedef PlanePipe<T, TX, TY + 3, PGRAD> Pipe;
-  static constexpr int NT = TX * TY;
-  static constexpr size_t SMEM = 128 + (size_t)Pipe::ELEMS * sizeof(T) + (size_t)(2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T) + 8 * Pipe::NS + 16;
+// Arguments of k_stage3d_tma.  Every global operand is given as one base pointer PER COMPONENT (interior
+// origin of that component), so an access is `base[a] + byte offset of the cell`: the bases live in the
+// constant bank and the only per-thread address state is one 64-bit byte offset advanced by one plane
+// per iteration.
+template <typename T>
+struct TmaStageArgs {
+  const T *u0[3];     // ustart
+  const T *sadd[3];   // closure term s (SADD)
+  const T *force[3];  // stored body force (nullable: force[0] == nullptr)
+  T *kout[3];         // k_i (GEN: nullable)
+  T *unew[3];         // u'
+  T *div;             // divergence(u') * Omega
+  const T *kin[INSB200_MAX_STAGES];  // GEN: earlier stage derivatives (component 0; + a*sc elements)
+  T coef[INSB200_MAX_STAGES];
+  int nk;
+  T coef_self;
+  i64 sy, sz, sc;     // strides in elements
 };
 
-// Global addressing inside the kernel uses 32-bit element offsets (the host checks 3*ccomp < 2^31):
-// one IMAD.WIDE per access instead of a 64-bit add chain.
-template <typename T, bool PGRAD, bool SADD, int TX, int TY>
+template <typename T, bool PGRAD, int TX, int TY, int NS>
+struct StageCfg {
+  typedef PlanePipe<T, TX, TY + 3, PGRAD, NS> Pipe;
+  static constexpr int NT = TX * TY;
+  static constexpr size_t SMEM = 128 + (size_t)Pipe::ELEMS * sizeof(T) + (size_t)(2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T) + 8 * NS + 16;
+};
+
+template <typename T>
+__device__ __forceinline__ T ld_off(const T *base, size_t ob) {
+  return __ldg(reinterpret_cast<const T *>(reinterpret_cast<const char *>(base) + ob));
+}
+template <typename T>
+__device__ __forceinline__ void st_off(T *base, size_t ob, T v) {
+  *reinterpret_cast<T *>(reinterpret_cast<char *>(base) + ob) = v;
+}
+
+// PGRAD: projection of the previous stage applied on load; !PGRAD: first stage, ustart is the tile itself.
+// SADD: closure term added.  GEN: general tableau row (runtime list of earlier k_j, k_i optional);
+// !GEN: the common row with a single entry (k_i stored, no earlier k_j) -- RK44 stages 1..3.
+template <typename T, bool PGRAD, bool SADD, bool GEN, int TX, int TY, int NS>
 __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
-    k_stage3d_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p, StageArgs<T> A, Geo g,
-                  T visc, Rh<T> rh, T vol, int zc, int ox, int oy, int oz) {
-  typedef StageCfg<T, PGRAD, SADD, TX, TY> Cfg;
+    k_stage3d_tma(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p,
+                  const __grid_constant__ TmaStageArgs<T> A, Geo g, T visc, Rh<T> rh, T vol, int zc, int ox, int oy, int oz) {
+  typedef StageCfg<T, PGRAD, TX, TY, NS> Cfg;
   typedef typename Cfg::Pipe Pipe;
-  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL, NS = Pipe::NS;
+  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL;
   constexpr int POFF = Pipe::POFF, PSLOT = Pipe::PSLOT, PEND = POFF + Pipe::NPS * PSLOT;
+  constexpr bool U0TILE = !PGRAD;
   extern __shared__ unsigned char smem_raw[];
   unsigned char *sb = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   T *su = reinterpret_cast<T *>(sb);
@@ -172,16 +203,11 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
   const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
   const int kbeg = blockIdx.z * zc, kend = min(kbeg + zc, g.n[2]);
   const int n0 = g.n[0], n1 = g.n[1], n2 = g.n[2];
-  const unsigned sy = (unsigned)A.sy, sz = (unsigned)A.sz, sc = (unsigned)A.sc;
-  const T *__restrict__ pu0 = A.u0;
-  const T *__restrict__ pforce = A.force;
-  const T *__restrict__ psadd = A.sadd;
-  T *__restrict__ pkout = A.kout;
-  T *__restrict__ punew = A.unew;
-  T *__restrict__ pdiv = A.div;
-  const bool has_force = pforce != nullptr, has_kout = pkout != nullptr, u0_tile = A.u0_is_u != 0;
-  const int nk = A.nk;
+  const bool has_force = A.force[0] != nullptr;
+  const bool has_kout = !GEN || A.kout[0] != nullptr;
+  const int nk = GEN ? A.nk : 0;
   const T coef_self = A.coef_self;
+  const size_t szb = (size_t)A.sz * sizeof(T), scb = (size_t)A.sc * sizeof(T);
 
   // plane q <-> z = kbeg - 2 + q
   Pipe pipe;
@@ -202,116 +228,128 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
   __syncthreads();
 
   const int gi = i0 + tx, gj = j0 + ty;
-  const unsigned ocell = (unsigned)gj * sy + gi;
+  const size_t ocell = ((size_t)gj * A.sy + gi) * sizeof(T);
   // the extra point of some threads on the minus halo: warp 1 (first TY lanes): (-1, l) component x;
   // warp 2: (l, -1) component y  (two different warps on two different schedulers)
   const bool hx = tid >= 32 && tid < 32 + TY, hy = tid >= 64 && tid < 64 + TX;
   const bool hany = hx || hy;
   const int hlx = hx ? -1 : tid - 64, hly = hx ? tid - 32 : -1;
   const int hgi = wrapi(i0 + hlx, n0, 1), hgj = wrapi(j0 + hly, n1, 1);
-  const unsigned ohalo = (unsigned)hgj * sy + hgi + (hx ? 0u : sc);  // component offset included
+  const size_t ohalo = ((size_t)hgj * A.sy + hgi) * sizeof(T);
   const int ha = hx ? 0 : 1;
   const int c_own = (ty + 2) * BX + tx + XL;
   const int c_halo = hany ? (hly + 2) * BX + hlx + XL : c_own;
+  // halo threads: bases of their one component
+  const T *hb_u0 = hx ? A.u0[0] : A.u0[1];
+  const T *hb_s = hx ? A.sadd[0] : A.sadd[1];
+  const T *hb_f = hx ? A.force[0] : A.force[1];
 
-  // f (convection-diffusion) -> k_i and u' of one component at one cell; o = global offset incl. component
-  auto combine = [&](T f, const unsigned o, const T uc, const T l_u0, const T l_s, const T l_f, T &f_out) -> T {
+  // f (convection-diffusion) -> k_i and u' of component a at the cell with byte offset ob
+  auto combine = [&](T f, const int a, const size_t ob, const T uc, const T l_u0, const T l_s, const T l_f, T &f_out) -> T {
     if (has_force) f = f + l_f;
     if (SADD) f = f + l_s;
     f_out = f;
-    T acc = u0_tile ? uc : l_u0;
-    for (int q = 0; q < nk; q++) acc = acc + A.coef[q] * __ldg(A.kin[q] + o);
+    T acc = U0TILE ? uc : l_u0;
+    if (GEN)
+      for (int q = 0; q < nk; q++) acc = acc + A.coef[q] * ld_off(A.kin[q], ob + a * scb);
     return acc + coef_self * f;
   };
 
   // u'_z of plane kbeg-1 (for the z-difference of the divergence on the first plane of the chunk)
   T uz_prev = T(0);
   const bool have_prev = kbeg > 0 || g.wrap[2];  // otherwise plane 0 is completed by k_divergence_planes
-  if (pdiv && have_prev) {
+  if (have_prev) {
     const int kz = wrapi(kbeg - 1, n2, g.wrap[2]);
-    const unsigned o = (unsigned)kz * sz + ocell + 2u * sc;
+    const size_t ob = (size_t)kz * szb + ocell;
     PlaneAcc<T, BX, UPL> U{su, Pipe::uoff(0) + c_own, Pipe::uoff(1) + c_own, Pipe::uoff(2) + c_own};
-    const T l_u0 = u0_tile ? T(0) : __ldg(pu0 + o);
-    const T l_s = SADD ? __ldg(psadd + o) : T(0);
-    const T l_f = has_force ? __ldg(pforce + o) : T(0);
+    const T l_u0 = U0TILE ? T(0) : ld_off(A.u0[2], ob);
+    const T l_s = SADD ? ld_off(A.sadd[2], ob) : T(0);
+    const T l_f = has_force ? ld_off(A.force[2], ob) : T(0);
     T f;
-    uz_prev = combine(convdiff_comp<T, 3, true, true>(U, 2, visc, rh.v), o, U(2, 0, 0, 0), l_u0, l_s, l_f, f);
+    uz_prev = combine(convdiff_comp<T, 3, true, true>(U, 2, visc, rh.v), 2, ob, U(2, 0, 0, 0), l_u0, l_s, l_f, f);
   }
   __syncthreads();  // plane 0 is retired: its slot takes plane NS
   if (tid == 0 && NS <= qlast) pipe.issue(NS);
 
-  int s_m = Pipe::uoff(1), s_0 = Pipe::uoff(2), s_p = Pipe::uoff(3), s_n = Pipe::uoff(0);  // planes q-1, q, q+1, q+2 at q = 2
-  int pa = Pipe::poff(4), pb = Pipe::poff(5);                                             // pressure planes q+2, q+3
-  unsigned o = (unsigned)kbeg * sz + ocell, oh = (unsigned)kbeg * sz + ohalo;
+  // slot offsets of planes q-1, q, q+1, q+2 [, q+3] at q = 2, rotated every iteration
+  int so[NS];
+#pragma unroll
+  for (int i = 0; i < NS; i++) so[i] = Pipe::uoff(1 + i);
+  int ws = 4 % NS;                       // barrier slot and parity of plane q+2
+  uint32_t wp = (uint32_t)((4 / NS) & 1);
+  int pa = Pipe::poff(4), pb = Pipe::poff(5);  // pressure planes q+2, q+3
+  size_t ob = (size_t)kbeg * szb + ocell, obh = (size_t)kbeg * szb + ohalo;
+
   // global operands (ustart, closure term, force) are software-pipelined one plane ahead in registers:
-  // requested as one batch before the barrier of iteration k-1, consumed at the end of iteration k
+  // requested as one batch before the barrier of iteration k-1, consumed in iteration k
   T n_u0[3], n_s[3], n_f[3], nh_u0 = T(0), nh_s = T(0), nh_f = T(0);
-  auto fetch_operands = [&](const unsigned oo, const unsigned ooh) {
+  auto fetch_operands = [&](const size_t o1, const size_t o1h) {
 #pragma unroll
     for (int a = 0; a < 3; a++) {
-      n_u0[a] = u0_tile ? T(0) : __ldg(pu0 + oo + a * sc);
-      n_s[a] = SADD ? __ldg(psadd + oo + a * sc) : T(0);
-      n_f[a] = has_force ? __ldg(pforce + oo + a * sc) : T(0);
+      n_u0[a] = U0TILE ? T(0) : ld_off(A.u0[a], o1);
+      n_s[a] = SADD ? ld_off(A.sadd[a], o1) : T(0);
+      n_f[a] = has_force ? ld_off(A.force[a], o1) : T(0);
     }
-    if (pdiv && hany) {
-      if (!u0_tile) nh_u0 = __ldg(pu0 + ooh);
-      if (SADD) nh_s = __ldg(psadd + ooh);
-      if (has_force) nh_f = __ldg(pforce + ooh);
+    if (hany) {
+      if (!U0TILE) nh_u0 = ld_off(hb_u0, o1h);
+      if (SADD) nh_s = ld_off(hb_s, o1h);
+      if (has_force) nh_f = ld_off(hb_f, o1h);
     }
   };
-  fetch_operands(o, oh);
+  fetch_operands(ob, obh);
   for (int k = kbeg; k < kend; k++) {
     const int q = k - kbeg + 2;  // plane number of k
     T l_u0[3], l_s[3], l_f[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) { l_u0[a] = n_u0[a]; l_s[a] = n_s[a]; l_f[a] = n_f[a]; }
     const T h_u0 = nh_u0, h_s = nh_s, h_f = nh_f;
-    PlaneAcc<T, BX, UPL> U{su, s_m + c_own, s_0 + c_own, s_p + c_own};
+    PlaneAcc<T, BX, UPL> U{su, so[0] + c_own, so[1] + c_own, so[2] + c_own};
     T un[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) {
       T f;
-      un[a] = combine(convdiff_comp<T, 3, true, true>(U, a, visc, rh.v), o + a * sc, U(a, 0, 0, 0), l_u0[a], l_s[a], l_f[a], f);
-      if (has_kout) pkout[o + a * sc] = f;
-      punew[o + a * sc] = un[a];
+      un[a] = combine(convdiff_comp<T, 3, true, true>(U, a, visc, rh.v), a, ob, U(a, 0, 0, 0), l_u0[a], l_s[a], l_f[a], f);
+      if (has_kout) st_off(A.kout[a], ob, f);
+      st_off(A.unew[a], ob, un[a]);
     }
-    if (pdiv) {
-      T *bx = sdx + (k & 1) * TY * (TX + 1), *by = sdy + (k & 1) * (TY + 1) * TX;
-      bx[ty * (TX + 1) + tx + 1] = un[0];
-      by[(ty + 1) * TX + tx] = un[1];
-      if (hany) {
-        PlaneAcc<T, BX, UPL> Uh{su, s_m + c_halo, s_0 + c_halo, s_p + c_halo};
-        T f;
-        const T fc = hx ? convdiff_comp<T, 3, true, true>(Uh, 0, visc, rh.v) : convdiff_comp<T, 3, true, true>(Uh, 1, visc, rh.v);
-        const T v = combine(fc, oh, Uh(ha, 0, 0, 0), h_u0, h_s, h_f, f);
-        if (hx) bx[hly * (TX + 1)] = v;
-        else by[hlx] = v;
-      }
+    T *bx = sdx + (k & 1) * TY * (TX + 1), *by = sdy + (k & 1) * (TY + 1) * TX;
+    bx[ty * (TX + 1) + tx + 1] = un[0];
+    by[(ty + 1) * TX + tx] = un[1];
+    if (hany) {
+      PlaneAcc<T, BX, UPL> Uh{su, so[0] + c_halo, so[1] + c_halo, so[2] + c_halo};
+      T f;
+      const T fc = hx ? convdiff_comp<T, 3, true, true>(Uh, 0, visc, rh.v) : convdiff_comp<T, 3, true, true>(Uh, 1, visc, rh.v);
+      const T v = combine(fc, ha, obh, Uh(ha, 0, 0, 0), h_u0, h_s, h_f, f);
+      if (hx) bx[hly * (TX + 1)] = v;
+      else by[hlx] = v;
     }
     // plane k+2 for the next iteration
     if (k + 1 < kend) {
-      fetch_operands(o + sz, oh + sz);
-      pipe.wait(q + 2);
-      pipe.project(s_n, pa, pb, tid, NT, rh.v);
+      fetch_operands(ob + szb, obh + szb);
+      pipe.wait_slot(ws, wp);
+      pipe.project(so[3], pa, pb, tid, NT, rh.v);
     }
     __syncthreads();
-    // slot of plane k-1 is free now: request plane k+3
-    if (tid == 0 && q + 3 <= qlast) pipe.issue(q + 3);
-    if (pdiv && (k > kbeg || have_prev)) {
-      const T *bx = sdx + (k & 1) * TY * (TX + 1), *by = sdy + (k & 1) * (TY + 1) * TX;
+    // slot of plane k-1 is free now: request plane k-1+NS
+    if (tid == 0 && q - 1 + NS <= qlast) pipe.issue(q - 1 + NS);
+    if (k > kbeg || have_prev) {
       T d = T(0);
       d += (un[0] - bx[ty * (TX + 1) + tx]) * rh.v[0];
       d += (un[1] - by[ty * TX + tx]) * rh.v[1];
       d += (un[2] - uz_prev) * rh.v[2];
-      pdiv[o] = d * vol;
+      st_off(A.div, ob, d * vol);
     }
     uz_prev = un[2];
-    const int t = s_m;
-    s_m = s_0; s_0 = s_p; s_p = s_n; s_n = t;
+    const int t = so[0];
+#pragma unroll
+    for (int i = 0; i + 1 < NS; i++) so[i] = so[i + 1];
+    so[NS - 1] = t;
+    ws = ws + 1 == NS ? 0 : ws + 1;
+    wp ^= (ws == 0) ? 1u : 0u;
     pa = pb;
     pb = pb + PSLOT == PEND ? POFF : pb + PSLOT;
-    o += sz;
-    oh += sz;
+    ob += szb;
+    obh += szb;
   }
 }
 
@@ -333,7 +371,7 @@ struct SigmaAcc {
 
 template <typename T, bool PGRAD, int TX, int TY>
 struct SmagCfg {
-  typedef PlanePipe<T, TX, TY + 4, PGRAD> Pipe;
+  typedef PlanePipe<T, TX, TY + 4, PGRAD, 4> Pipe;
   static constexpr int NT = TX * TY;
   static constexpr int SX = TX + 2, SY = TY + 2, SPL = SX * SY, SSLOT = 6 * SPL;
   static constexpr size_t SMEM = 128 + (size_t)(Pipe::ELEMS + 3 * SSLOT) * sizeof(T) + 8 * Pipe::NS + 16;
