@@ -241,6 +241,10 @@ def kernel_words(D, smag, force, nstages=4):
         "momentum_stage": ((nstages - 1) * 4.0 * D + (3.0 + nstages - 1) * D) / nstages
                           + (D if force else 0) + (ntens if smag else 0),
         "smagtensor": D + ntens,
+        # TMA path (3-D): first stage R u, W k, W u', W div; middle stages + R ustart, R p; last stage (RK44) R u, R p,
+        # R ustart, R k_1..k_{s-1}, W u', W div; "momentum_stage" is the launch-weighted mean of first + middle stages
+        "momentum_stage_last": 2.0 * D + 2 + D * (nstages - 1) + D + (D if force else 0) + (D if smag else 0),
+        "smagorinsky_fused": 2.0 * D + 1,  # R u, R p, W s (sigma never leaves shared memory)
         "divergence": D + 1.0,
         "pressure_gradient": 2.0 * D + 1,
         "poisson_scale": 2.0,          # half spectrum of complex words, read + written

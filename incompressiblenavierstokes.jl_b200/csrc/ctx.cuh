@@ -53,12 +53,13 @@ struct Geo {
 enum TimerId {
   TM_IMPORT = 0, TM_EXPORT, TM_BC, TM_MOMENTUM, TM_STAGE, TM_SMAGTENSOR, TM_DIVTENSOR, TM_DIVERGENCE,
   TM_FFT_FWD, TM_FFT_INV, TM_POISSON_SCALE, TM_GRADIENT, TM_REDUCE, TM_HALO, TM_PACK, TM_A2A,
-  TM_MISC, TM_COUNT
+  TM_MISC, TM_STAGE_GEN, TM_SMAG_FUSED, TM_GHOSTS, TM_COUNT
 };
 static const char *const kTimerNames[TM_COUNT] = {
     "import_ghosted", "export_ghosted", "apply_bc", "momentum", "momentum_stage", "smagtensor",
     "divoftensor", "divergence", "cufft_forward", "cufft_inverse", "poisson_scale", "pressure_gradient",
-    "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc"};
+    "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc", "momentum_stage_last", "smagorinsky_fused",
+    "fill_ghosts"};
 
 struct TimerRec {
   cudaEvent_t a, b;

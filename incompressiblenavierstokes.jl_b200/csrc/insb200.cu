@@ -376,7 +376,7 @@ template <typename T>
 static int fill_ghosts(insb200_ctx *c, void *base, int nc, int wm, int wp) {
   if (!c->padded) return 0;
   {
-    ScopedTimer tm(c, TM_BC);
+    ScopedTimer tm(c, TM_GHOSTS);
     const int gm = c->gm, gp = c->gp, gw = gm + gp;
     const int n0 = c->nloc[0], n1 = c->nloc[1], n2 = c->nloc[2];
     const int fill_z = c->nranks == 1;
@@ -1015,7 +1015,7 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
 // s = smagorinsky_closure(u) into c->sbuf (interior) from the padded velocity buffer (ghosts valid, 2 layers)
 template <typename T>
 static int launch_smag_tma(insb200_ctx *c, double theta, const void *ubase, const void *pbase) {
-  ScopedTimer tm(c, TM_SMAGTENSOR);
+  ScopedTimer tm(c, TM_SMAG_FUSED);
   Geo g = geo_compact(c);
   T *sout = (T *)c->sbuf + c->corg;
   if (pbase) return launch_smag_tma_i<T, true>(c, sout, g, eddy_const<T>(c, theta), make_rh<T>(c), ubase, pbase);
@@ -1115,14 +1115,14 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
     a.nk = 0;
     for (int j = 0; j < i; j++) {
       if (tb.A[i * tb.s + j] == 0.0) continue;  // exact: adds +-0
-      a.kin[a.nk] = (const T *)c->kbuf[j] + goff;
+      for (int q = 0; q < 3; q++) a.kin[a.nk][q] = (const T *)c->kbuf[j] + goff + q * c->ccomp;
       a.coef[a.nk] = T(dt) * T(tb.A[i * tb.s + j]);  // `dt * A[i,j]` formed first (:37)
       a.nk++;
     }
     a.coef_self = T(dt) * T(tb.A[i * tb.s + i]);
     a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp;
     {
-      ScopedTimer tm(c, TM_STAGE);
+      ScopedTimer tm(c, (a.nk > 0 || !a.kout[0]) ? TM_STAGE_GEN : TM_STAGE);
       INS_TRY((launch_stage_tma<T>(c, a, g, visc, rh, c->ubuf[cur], pbase)));
     }
     // apply_bc_u! (:48): ghosts of u' for the next stage's boxes (and, multi-rank, for the first plane's divergence)

@@ -157,7 +157,7 @@ struct TmaStageArgs {
   T *kout[3];         // k_i (GEN: nullable)
   T *unew[3];         // u'
   T *div;             // divergence(u') * Omega
-  const T *kin[INSB200_MAX_STAGES];  // GEN: earlier stage derivatives (component 0; + a*sc elements)
+  const T *kin[INSB200_MAX_STAGES][3];  // GEN: earlier stage derivatives k_j, per component
   T coef[INSB200_MAX_STAGES];
   int nk;
   T coef_self;
@@ -192,6 +192,7 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
   constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL;
   constexpr int POFF = Pipe::POFF, PSLOT = Pipe::PSLOT, PEND = POFF + Pipe::NPS * PSLOT;
   constexpr bool U0TILE = !PGRAD;
+  constexpr int NKP = GEN ? 3 : 1;  // earlier k_j prefetched in registers (RK44's last row has 3)
   extern __shared__ unsigned char smem_raw[];
   unsigned char *sb = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
   T *su = reinterpret_cast<T *>(sb);
@@ -245,13 +246,19 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
   const T *hb_f = hx ? A.force[0] : A.force[1];
 
   // f (convection-diffusion) -> k_i and u' of component a at the cell with byte offset ob
-  auto combine = [&](T f, const int a, const size_t ob, const T uc, const T l_u0, const T l_s, const T l_f, T &f_out) -> T {
+  // (the first NKP earlier derivatives k_j arrive prefetched in l_k; further ones are read in place)
+  auto combine = [&](T f, const int a, const size_t ob, const T uc, const T l_u0, const T l_s, const T l_f,
+                     const T (&l_k)[NKP], T &f_out) -> T {
     if (has_force) f = f + l_f;
     if (SADD) f = f + l_s;
     f_out = f;
     T acc = U0TILE ? uc : l_u0;
-    if (GEN)
-      for (int q = 0; q < nk; q++) acc = acc + A.coef[q] * ld_off(A.kin[q], ob + a * scb);
+    if (GEN) {
+#pragma unroll
+      for (int q = 0; q < NKP; q++)
+        if (q < nk) acc = acc + A.coef[q] * l_k[q];
+      for (int q = NKP; q < nk; q++) acc = acc + A.coef[q] * ld_off(a == 0 ? A.kin[q][0] : (a == 1 ? A.kin[q][1] : A.kin[q][2]), ob);
+    }
     return acc + coef_self * f;
   };
 
@@ -265,8 +272,11 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
     const T l_u0 = U0TILE ? T(0) : ld_off(A.u0[2], ob);
     const T l_s = SADD ? ld_off(A.sadd[2], ob) : T(0);
     const T l_f = has_force ? ld_off(A.force[2], ob) : T(0);
+    T l_k[NKP];
+#pragma unroll
+    for (int q = 0; q < NKP; q++) l_k[q] = (GEN && q < nk) ? ld_off(A.kin[q][2], ob) : T(0);
     T f;
-    uz_prev = combine(convdiff_comp<T, 3, true, true>(U, 2, visc, rh.v), 2, ob, U(2, 0, 0, 0), l_u0, l_s, l_f, f);
+    uz_prev = combine(convdiff_comp<T, 3, true, true>(U, 2, visc, rh.v), 2, ob, U(2, 0, 0, 0), l_u0, l_s, l_f, l_k, f);
   }
   __syncthreads();  // plane 0 is retired: its slot takes plane NS
   if (tid == 0 && NS <= qlast) pipe.issue(NS);
@@ -282,33 +292,46 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
 
   // global operands (ustart, closure term, force) are software-pipelined one plane ahead in registers:
   // requested as one batch before the barrier of iteration k-1, consumed in iteration k
-  T n_u0[3], n_s[3], n_f[3], nh_u0 = T(0), nh_s = T(0), nh_f = T(0);
+  T n_u0[3], n_s[3], n_f[3], n_k[3][NKP], nh_u0 = T(0), nh_s = T(0), nh_f = T(0), nh_k[NKP];
+#pragma unroll
+  for (int q = 0; q < NKP; q++) nh_k[q] = T(0);
   auto fetch_operands = [&](const size_t o1, const size_t o1h) {
 #pragma unroll
     for (int a = 0; a < 3; a++) {
       n_u0[a] = U0TILE ? T(0) : ld_off(A.u0[a], o1);
       n_s[a] = SADD ? ld_off(A.sadd[a], o1) : T(0);
       n_f[a] = has_force ? ld_off(A.force[a], o1) : T(0);
+#pragma unroll
+      for (int q = 0; q < NKP; q++) n_k[a][q] = (GEN && q < nk) ? ld_off(A.kin[q][a], o1) : T(0);
     }
     if (hany) {
       if (!U0TILE) nh_u0 = ld_off(hb_u0, o1h);
       if (SADD) nh_s = ld_off(hb_s, o1h);
       if (has_force) nh_f = ld_off(hb_f, o1h);
+#pragma unroll
+      for (int q = 0; q < NKP; q++)
+        if (GEN && q < nk) nh_k[q] = ld_off(hx ? A.kin[q][0] : A.kin[q][1], o1h);
     }
   };
   fetch_operands(ob, obh);
   for (int k = kbeg; k < kend; k++) {
     const int q = k - kbeg + 2;  // plane number of k
-    T l_u0[3], l_s[3], l_f[3];
+    T l_u0[3], l_s[3], l_f[3], l_k[3][NKP], h_k[NKP];
 #pragma unroll
-    for (int a = 0; a < 3; a++) { l_u0[a] = n_u0[a]; l_s[a] = n_s[a]; l_f[a] = n_f[a]; }
+    for (int a = 0; a < 3; a++) {
+      l_u0[a] = n_u0[a]; l_s[a] = n_s[a]; l_f[a] = n_f[a];
+#pragma unroll
+      for (int q = 0; q < NKP; q++) l_k[a][q] = n_k[a][q];
+    }
+#pragma unroll
+    for (int q = 0; q < NKP; q++) h_k[q] = nh_k[q];
     const T h_u0 = nh_u0, h_s = nh_s, h_f = nh_f;
     PlaneAcc<T, BX, UPL> U{su, so[0] + c_own, so[1] + c_own, so[2] + c_own};
     T un[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) {
       T f;
-      un[a] = combine(convdiff_comp<T, 3, true, true>(U, a, visc, rh.v), a, ob, U(a, 0, 0, 0), l_u0[a], l_s[a], l_f[a], f);
+      un[a] = combine(convdiff_comp<T, 3, true, true>(U, a, visc, rh.v), a, ob, U(a, 0, 0, 0), l_u0[a], l_s[a], l_f[a], l_k[a], f);
       if (has_kout) st_off(A.kout[a], ob, f);
       st_off(A.unew[a], ob, un[a]);
     }
@@ -319,7 +342,7 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
       PlaneAcc<T, BX, UPL> Uh{su, so[0] + c_halo, so[1] + c_halo, so[2] + c_halo};
       T f;
       const T fc = hx ? convdiff_comp<T, 3, true, true>(Uh, 0, visc, rh.v) : convdiff_comp<T, 3, true, true>(Uh, 1, visc, rh.v);
-      const T v = combine(fc, ha, obh, Uh(ha, 0, 0, 0), h_u0, h_s, h_f, f);
+      const T v = combine(fc, ha, obh, Uh(ha, 0, 0, 0), h_u0, h_s, h_f, h_k, f);
       if (hx) bx[hly * (TX + 1)] = v;
       else by[hlx] = v;
     }
