@@ -234,17 +234,14 @@ def cpu_sample(wl, steps=1, n=None):
 
 # words (sizeof(T)) per cell per LAUNCH of each library kernel: the algorithmic minimum, every
 # logical field read / written once (DESIGN.md "Kernels and rooflines")
-def kernel_words(D, smag, force, nstages=4):
+def kernel_words(D, smag, force, nstages=4, tma=False):
+    """Algorithmic words per cell per LAUNCH of each library kernel (every logical field read / written once)."""
     ntens = D * (D + 1) // 2
-    return {
-        # stages 1..s-1: R u, R ustart, W k, W u' (4D); last stage: R u, R ustart, R k_1..k_{s-1}, W u'
-        "momentum_stage": ((nstages - 1) * 4.0 * D + (3.0 + nstages - 1) * D) / nstages
-                          + (D if force else 0) + (ntens if smag else 0),
+    extra = (D if force else 0)
+    w = {
+        # 2-D / generic path: stages 1..s-1: R u, R ustart, W k, W u' (4D); last stage: R u, R ustart, R k_1..k_{s-1}, W u'
+        "momentum_stage": ((nstages - 1) * 4.0 * D + (3.0 + nstages - 1) * D) / nstages + extra + (ntens if smag else 0),
         "smagtensor": D + ntens,
-        # TMA path (3-D): first stage R u, W k, W u', W div; middle stages + R ustart, R p; last stage (RK44) R u, R p,
-        # R ustart, R k_1..k_{s-1}, W u', W div; "momentum_stage" is the launch-weighted mean of first + middle stages
-        "momentum_stage_last": 2.0 * D + 2 + D * (nstages - 1) + D + (D if force else 0) + (D if smag else 0),
-        "smagorinsky_fused": 2.0 * D + 1,  # R u, R p, W s (sigma never leaves shared memory)
         "divergence": D + 1.0,
         "pressure_gradient": 2.0 * D + 1,
         "poisson_scale": 2.0,          # half spectrum of complex words, read + written
@@ -253,6 +250,25 @@ def kernel_words(D, smag, force, nstages=4):
         "import_ghosted": 2.0 * D,
         "export_ghosted": 2.0 * D,
     }
+    if tma:
+        # 3-D TMA path: the stage kernel also writes the Poisson right-hand side (W div) and applies the previous
+        # projection on load (R p).  first stage: R u, W k, W u', W div; middle stages: + R ustart, R p
+        first, mid = 3.0 * D + 1, 4.0 * D + 2
+        sadd = (D if smag else 0)  # closure term s read by the stage kernel
+        w["momentum_stage"] = (first + (nstages - 2) * mid) / (nstages - 1) + extra + sadd
+        # last stage: R u, R p, R ustart, R k_1..k_{s-1}, W u', W div
+        w["momentum_stage_last"] = 3.0 * D + 2 + D * (nstages - 1) + extra + sadd
+        # R u, R p (all but the first stage), W s; sigma never leaves shared memory
+        w["smagorinsky_fused"] = 2.0 * D + (nstages - 1.0) / nstages
+    return w
+
+
+# DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of one `ncu --set full` capture at the
+# default workload size; see profiles/r1_ncu_full_tma_kernels.txt
+NCU_TRAFFIC = {
+    ("dt3d_smag", 512, "smagorinsky_fused"): 2.524938e9 + 1.580448e9,
+    ("dt3d_smag", 512, "momentum_stage"): 5.969720e9 + 3.732034e9,
+}
 
 
 def run_reference(args, wl):
@@ -383,7 +399,7 @@ def run_ours(args, wl):
     setup.ctx.call("insb200_set_profiling", 0)
     esz = np.dtype(T).itemsize
     cells_local = cells / world
-    words = kernel_words(D, theta is not None, wl["force"])
+    words = kernel_words(D, theta is not None, wl["force"], tma=(D == 3 and base_n % 32 == 0))
     peak, peak_src = peaks()
     kern = {}
     for name, (tms, cnt) in timers.items():
@@ -396,7 +412,8 @@ def run_ours(args, wl):
     roofline = None
     if dom:
         roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["alg_GBs"], "peak": peak, "unit": "GB/s",
-                    "frac": kern[dom]["frac"], "traffic": None, "peak_source": peak_src,
+                    "frac": kern[dom]["frac"], "traffic": NCU_TRAFFIC.get((args.workload, base_n, dom)),
+                    "peak_source": peak_src,
                     "alg_bytes_per_launch": words[dom] * esz * cells_local,
                     "ms_per_launch": kern[dom]["ms_per_launch"],
                     "share_of_step": kern[dom]["ms_per_step"] / sum(v["ms_per_step"] for v in kern.values())}
