@@ -60,13 +60,21 @@ def init_distributed():
     torch.cuda.set_device(local)
     if not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return B200Backend(device=local, rank=rank, nranks=world, nccl_id=_fresh_nccl_id(rank, local))
+
+
+def _fresh_nccl_id(rank, device):
+    """A new NCCL unique id from rank 0, broadcast over torch.distributed: every communicator (one per
+    context) needs its own."""
+    import torch.distributed as dist
+
     lib = _lib.load()
     buf = (C.c_ubyte * 128)()
     if rank == 0:
         _lib.check(lib, None, lib.insb200_comm_unique_id(buf))
-    t = torch.tensor(list(bytes(buf)), dtype=torch.uint8, device=f"cuda:{local}")
+    t = torch.tensor(list(bytes(buf)), dtype=torch.uint8, device=f"cuda:{device}")
     dist.broadcast(t, 0)
-    return B200Backend(device=local, rank=rank, nranks=world, nccl_id=bytes(t.cpu().tolist()))
+    return bytes(t.cpu().tolist())
 
 
 # --------------------------------------------------------------------------------------------
@@ -79,7 +87,10 @@ class _Ctx:
         nn = (C.c_int * 3)(*([int(v) for v in n] + [1] * (3 - D)))
         hh = (C.c_double * 3)(*([float(v) for v in h] + [1.0] * (3 - D)))
         idbuf = None
-        if backend.nccl_id is not None:
+        if backend.nranks > 1:
+            if getattr(backend, "_id_used", False):  # a unique id serves exactly one communicator
+                backend.nccl_id = _fresh_nccl_id(backend.rank, backend.device)
+            backend._id_used = True
             idbuf = (C.c_ubyte * 128).from_buffer_copy(backend.nccl_id)
         rc = self.lib.insb200_create(C.byref(self.h), D, nn, 0 if dtype == np.float32 else 1, hh, float(Re),
                                      backend.device, backend.rank, backend.nranks, idbuf)
@@ -91,11 +102,16 @@ class _Ctx:
         rc = getattr(self.lib, name)(self.h, *args)
         _lib.check(self.lib, self.h, rc)
 
+    def close(self):
+        """insb200_destroy: frees the workspace, plans and the NCCL communicator.  With nranks > 1 call it on
+        every rank at the same point of the program (communicator teardown)."""
+        if getattr(self, "h", None):
+            self.lib.insb200_destroy(self.h)
+            self.h = None
+
     def __del__(self):
         try:
-            if getattr(self, "h", None):
-                self.lib.insb200_destroy(self.h)
-                self.h = None
+            self.close()
         except Exception:
             pass
 

@@ -38,7 +38,11 @@ def main():
     rank, world = backend.rank, backend.nranks
     torch.cuda.set_device(backend.device)
     failures = 0
-    for n, T, force, theta, nsteps, dt in CASES:
+    import faulthandler
+    sel = os.environ.get("MGPU_CASES")
+    cases = [CASES[int(i)] for i in sel.split(",")] if sel else CASES
+    for n, T, force, theta, nsteps, dt in cases:
+        faulthandler.dump_traceback_later(90, exit=True)  # a hung collective must not burn the GPU budget
         D = len(n)
         if n[D - 1] % world or n[D - 1] // world < 4:
             continue
@@ -72,6 +76,10 @@ def main():
             print(f"[mgpu x{world}] n={n} {np.dtype(T).name} force={force} theta={theta}: rel_l2(u)={err:.3e} "
                   f"ke_err={kerr:.3e} max|div|={np.abs(div[sc.grid.Ip]).max():.2e} -> {'ok' if ok else 'FAIL'}", flush=True)
             failures += not ok
+        torch.cuda.synchronize()
+        dist.barrier()
+        sc.ctx.close()  # same program point on every rank
+    faulthandler.cancel_dump_traceback_later()
     f = torch.tensor([failures], device=f"cuda:{backend.device}")
     dist.broadcast(f, 0)
     dist.barrier()
