@@ -87,6 +87,8 @@ struct insb200_ctx {
   int ext[3] = {1, 1, 1};  // padded extents PX, PY, PZ
   int gm = 0, gp = 0;      // ghost layers kept valid on the minus / plus side (y, z; x has more room)
   int fuse_gradient = 1;   // apply the projection of stage i in the loader of stage i+1
+  int zcols = 0, zthreads = 384;  // k_zsolve tuning: columns per tile (0 = largest that fits 64 KB), threads per block
+  int zsolve = 1;          // 3-D: own fused last-axis transform + symbol kernel instead of cuFFT's z passes
   cudaStream_t stream = nullptr;
   cudaStream_t own_stream = nullptr;
   ncclComm_t comm = nullptr;
@@ -113,6 +115,7 @@ struct insb200_ctx {
   void *pcplx = nullptr;                                // complex spectrum
   void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
   void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)
+  void *ztw = nullptr;                                  // twiddles exp(-2 pi i t / n_last) of k_zsolve (complex T)
   void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)
   void *hostio = nullptr;                               // reference-layout device image for *_host calls
   void *red = nullptr;                                  // reduction partials (double)

@@ -11,6 +11,7 @@
 #include "stencil.cuh"
 #include "tiled.cuh"
 #include "tma_stage.cuh"
+#include "zsolve.cuh"
 
 namespace insb200 {
 thread_local std::string g_create_error;
@@ -265,7 +266,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio, c->ztw};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -331,6 +332,16 @@ static int ensure_fft(insb200_ctx *c) {
     }
     INS_CUFFT(c, cufftSetStream(c->plan_fwd, c->stream));
     INS_CUFFT(c, cufftSetStream(c->plan_inv, c->stream));
+    if (D == 3) {  // batched in-plane transforms for the k_zsolve path
+      int nn[2] = {c->nloc[1], c->nloc[0]};
+      int remb[2] = {c->ext[1], c->ext[0]};
+      int cemb[2] = {c->nloc[1], c->nxh};
+      const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxh;
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
+      INS_CUFFT(c, cufftSetStream(c->plan_fwd_in, c->stream));
+      INS_CUFFT(c, cufftSetStream(c->plan_inv_in, c->stream));
+    }
   } else {
     // rows of the in-slab spectrum: 3-D: ny*nzl, 2-D: nyl
     const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
@@ -475,6 +486,80 @@ static int bc_fill(insb200_ctx *c, void *base, int nc) {
   return 0;
 }
 
+// ---- fused last-axis transform + symbol + inverse (zsolve.cuh) --------------------------------------
+static bool zsolve_supported(const insb200_ctx *c) {
+  const int nz = c->nglob[2];
+  return c->D == 3 && c->zsolve && nz >= 8 && nz <= 2048 && (nz & (nz - 1)) == 0;
+}
+
+template <typename T, int COLS>
+static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad) {
+  const int nz = c->nglob[2];
+  const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + 16;
+  auto kern = k_zsolve<T, COLS>;
+  // 2-D descriptor of the spectrum seen as [nz][2*ncols] words of T, box = (2*COLS) x min(nz, 256)
+  CUtensorMap tm;
+  {
+    auto key = std::make_tuple((const void *)S, -COLS, (int)(ncols & 0x7fffffff));
+    auto it = c->tmaps.find(key);
+    if (it != c->tmaps.end()) tm = it->second;
+    else {
+      void *fn = nullptr;
+      cudaDriverEntryPointQueryResult qr;
+      INS_CUDA(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+      if (!fn || qr != cudaDriverEntryPointSuccess) INS_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
+      cuuint64_t dims[2] = {(cuuint64_t)(2 * ncols), (cuuint64_t)nz};
+      cuuint64_t strides[1] = {(cuuint64_t)(2 * ncols) * sizeof(T)};
+      cuuint32_t box[2] = {(cuuint32_t)(2 * COLS), (cuuint32_t)std::min(nz, 256)};
+      cuuint32_t estr[2] = {1, 1};
+      CUresult r = ((PFN_tmap_encode)fn)(&tm, sizeof(T) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, S,
+                                         dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) INS_FAIL(c, "cuTensorMapEncodeTiled (spectrum) failed with CUresult " + std::to_string((int)r));
+      c->tmaps[key] = tm;
+    }
+  }
+  static size_t attr = 0;
+  if (smem > attr) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  const unsigned nb = (unsigned)((ncols + COLS - 1) / COLS);
+  kern<<<nb, c->zthreads, smem, c->stream>>>(tm, (const Cx<T> *)c->ztw, (const T *)c->ahat[0], (const T *)c->ahat[1],
+                                     (const T *)c->ahat[2], nz, ncols, nxw, kx0, invN, rad);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+// S: [z][ncols] spectrum with all nz points of the last axis local; columns c = ky*nxw + (kx - kx0)
+template <typename T>
+static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN) {
+  ScopedTimer tm(c, TM_POISSON_SCALE);
+  const int nz = c->nglob[2];
+  if (!c->ztw) {
+    std::vector<Cx<T>> tw(nz);
+    for (int t = 0; t < nz; t++) {
+      const double a = -2.0 * M_PI * (double)t / (double)nz;
+      tw[t] = Cx<T>{(T)std::cos(a), (T)std::sin(a)};
+    }
+    INS_TRY(dev_alloc(c, &c->ztw, nz * sizeof(Cx<T>)));
+    INS_CUDA(c, cudaMemcpyAsync(c->ztw, tw.data(), nz * sizeof(Cx<T>), cudaMemcpyHostToDevice, c->stream));
+    INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  }
+  ZRadix rad;
+  rad.n = 0;
+  int m = 0;
+  while ((1 << m) < nz) m++;
+  while (m >= 3) { rad.r[rad.n++] = 3; m -= 3; }  // log2 of the radix: 8, 8, .. then 4 or 2
+  if (m > 0) rad.r[rad.n++] = m;
+  const size_t col_bytes = (size_t)nz * sizeof(Cx<T>);
+  if (c->zcols == 4) return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
+  if (c->zcols == 8 && 8 * col_bytes <= 131072) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
+  if (16 * col_bytes <= 65536) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);
+  if (8 * col_bytes <= 65536) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
+  return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
+}
+
 // ---- spectral Poisson solve on the compact real buffer (in: preal interior = rhs; out: solution) --
 template <typename T, int D>
 static int poisson_solve(insb200_ctx *c) {
@@ -484,6 +569,22 @@ static int poisson_solve(insb200_ctx *c) {
   C *S = (C *)c->pcplx;
   const double ntot = (double)c->nglob[0] * c->nglob[1] * (D == 3 ? c->nglob[2] : 1);
   const T invN = T(1) / T(ntot);
+  if (c->nranks == 1 && D == 3 && zsolve_supported(c)) {
+    {
+      ScopedTimer tm(c, TM_FFT_FWD);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)pr, (cufftComplex *)S));
+      else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
+      c->fft_execs++;
+    }
+    INS_TRY((launch_zsolve<T>(c, S, (i64)c->nloc[1] * c->nxh, c->nxh, 0, invN)));
+    {
+      ScopedTimer tm(c, TM_FFT_INV);
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
+      else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
+      c->fft_execs++;
+    }
+    return 0;
+  }
   if (c->nranks == 1) {
     {
       ScopedTimer tm(c, TM_FFT_FWD);
@@ -533,7 +634,9 @@ static int poisson_solve(insb200_ctx *c) {
     }
     INS_NCCL(c, ncclGroupEnd());
   }
-  if (c->kxl > 0) {
+  if (c->kxl > 0 && D == 3 && zsolve_supported(c)) {
+    INS_TRY((launch_zsolve<T>(c, S, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
+  } else if (c->kxl > 0) {
     {
       ScopedTimer tm(c, TM_FFT_FWD);
       if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)S, (cufftComplex *)S, CUFFT_FORWARD));
@@ -1411,6 +1514,9 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
   else if (k == "zchunk") { if (v < 2) INS_FAIL(c, "zchunk must be >= 2"); c->zchunk = v; }
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
+  else if (k == "zsolve") c->zsolve = v != 0;
+  else if (k == "zcols") { if (v != 0 && v != 4 && v != 8 && v != 16) INS_FAIL(c, "zcols must be 0, 4, 8 or 16"); c->zcols = v; }
+  else if (k == "zthreads") { if (v < 64 || v > 512 || v % 32) INS_FAIL(c, "zthreads must be a multiple of 32 in [64, 512]"); c->zthreads = v; }
   else INS_FAIL(c, "unknown parameter: " + k);
   return 0;
 }

@@ -1,0 +1,198 @@
+// zsolve.cuh -- last-axis part of the spectral pressure solve in ONE pass over the half spectrum:
+//   forward FFT along z  ->  p^ = -p^ / ((ax+ay)+az) * (1/N), zero mode -> 0  ->  inverse FFT along z
+// (src/pressure.jl:323-344: mul!(phat, plan, pI); phat = -phat/(ax+ay+az); phat[1] = 0; ldiv!(pI, plan, phat)).
+// cuFFT does the batched in-plane (x, y) transforms; this kernel replaces cuFFT's z pass of the forward
+// transform, the symbol-scaling kernel and the z pass of the inverse transform (3 read+write passes over
+// the spectrum -> 1).
+//
+// A block owns COLS consecutive columns c = ky*nxw + kx of the spectrum (contiguous in memory for every z)
+// and all nz points of each: the tile [nz][COLS] sits in shared memory.  Forward = in-place
+// decimation-in-frequency passes of radix 8/4/2 (natural order in, digit-reversed order out); the symbol
+// is applied at digit-reversed positions; inverse = the adjoint passes in reverse order (digit-reversed in,
+// natural out).  No reordering pass, no second buffer.  Twiddles exp(-2 pi i t / nz) come from a table
+// computed in Float64 on the host.
+#pragma once
+#include "ctx.cuh"
+#include "tma_stage.cuh"
+
+namespace insb200 {
+
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *tm, uint64_t *bar, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                   smem_u32(dst)),
+               "l"(reinterpret_cast<uint64_t>(tm)), "r"(x), "r"(y), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, const void *src, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(x), "r"(y), "r"(smem_u32(src))
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit_wait() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+template <typename T> struct Cx { T x, y; };
+template <typename T> __device__ __forceinline__ Cx<T> cadd(Cx<T> a, Cx<T> b) { return {a.x + b.x, a.y + b.y}; }
+template <typename T> __device__ __forceinline__ Cx<T> csub(Cx<T> a, Cx<T> b) { return {a.x - b.x, a.y - b.y}; }
+// a * b, and a * conj(b)
+template <typename T, bool CONJ> __device__ __forceinline__ Cx<T> cmul(Cx<T> a, Cx<T> b) {
+  if (CONJ) return {a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y};
+  return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x};
+}
+// multiply by -i (forward) or +i (inverse)
+template <typename T, bool INV> __device__ __forceinline__ Cx<T> mul_mi(Cx<T> a) {
+  if (INV) return {-a.y, a.x};
+  return {a.y, -a.x};
+}
+
+// in-register R-point DFT, forward: y_q = sum_m x_m exp(-2 pi i m q / R); INV: conjugate kernel
+template <typename T, bool INV> __device__ __forceinline__ void dft2(Cx<T> (&v)[2]) {
+  const Cx<T> a = v[0], b = v[1];
+  v[0] = cadd(a, b);
+  v[1] = csub(a, b);
+}
+template <typename T, bool INV> __device__ __forceinline__ void dft4(Cx<T> (&v)[4]) {
+  const Cx<T> a = cadd(v[0], v[2]), b = csub(v[0], v[2]), c = cadd(v[1], v[3]), d = mul_mi<T, INV>(csub(v[1], v[3]));
+  v[0] = cadd(a, c);
+  v[1] = cadd(b, d);
+  v[2] = csub(a, c);
+  v[3] = csub(b, d);
+}
+template <typename T, bool INV> __device__ __forceinline__ void dft8(Cx<T> (&v)[8]) {
+  // two radix-4 on even / odd inputs, then the radix-2 combination with w8^q
+  Cx<T> e[4] = {v[0], v[2], v[4], v[6]}, o[4] = {v[1], v[3], v[5], v[7]};
+  dft4<T, INV>(e);
+  dft4<T, INV>(o);
+  const T h = T(0.70710678118654752440);
+  // w8^1 = (1 - i)/sqrt2 (forward), (1 + i)/sqrt2 (inverse); w8^2 = -i / +i; w8^3 = (-1 - i)/sqrt2 / (-1 + i)/sqrt2
+  const Cx<T> o1 = INV ? Cx<T>{(o[1].x - o[1].y) * h, (o[1].x + o[1].y) * h} : Cx<T>{(o[1].x + o[1].y) * h, (o[1].y - o[1].x) * h};
+  const Cx<T> o2 = mul_mi<T, INV>(o[2]);
+  const Cx<T> o3 = INV ? Cx<T>{(-o[3].x - o[3].y) * h, (o[3].x - o[3].y) * h} : Cx<T>{(o[3].y - o[3].x) * h, (-o[3].x - o[3].y) * h};
+  v[0] = cadd(e[0], o[0]); v[4] = csub(e[0], o[0]);
+  v[1] = cadd(e[1], o1);   v[5] = csub(e[1], o1);
+  v[2] = cadd(e[2], o2);   v[6] = csub(e[2], o2);
+  v[3] = cadd(e[3], o3);   v[7] = csub(e[3], o3);
+}
+template <typename T, int R, bool INV> __device__ __forceinline__ void dftR(Cx<T> (&v)[R]) {
+  if constexpr (R == 2) dft2<T, INV>(v);
+  else if constexpr (R == 4) dft4<T, INV>(v);
+  else dft8<T, INV>(v);
+}
+
+// one in-place pass over the tile s[nz][COLS] for blocks of length L = R << lsub (sub-stride 1 << lsub).
+//   forward (DIF):  y_q = DFT_R(x)_q * w_L^{j q}          inverse (DIT): y_m = IDFT_R(x_q * conj(w_L^{j q}))_m
+// All sizes are powers of two: index arithmetic is shifts and masks.
+template <typename T, int R, bool INV, int COLS>
+__device__ __forceinline__ void zpass(Cx<T> *s, const Cx<T> *tw, int nz, int lsub, int tid, int nt) {
+  constexpr int LR = R == 8 ? 3 : (R == 4 ? 2 : 1), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
+  const int sub = 1 << lsub, nw = (nz >> LR) << LC;
+  int ltstep = 0;  // log2(nz / L)
+  while ((R << lsub << ltstep) < nz) ltstep++;
+#pragma unroll 2
+  for (int w = tid; w < nw; w += nt) {
+    const int col = w & (COLS - 1), jb = w >> LC;
+    const int b = jb >> lsub, j = jb & (sub - 1);
+    Cx<T> *p = s + ((((b << LR) << lsub) + j) << LC) + col;
+    const int st = sub << LC;
+    Cx<T> v[R];
+#pragma unroll
+    for (int m = 0; m < R; m++) v[m] = p[m * st];
+    const int jt = j << ltstep;
+    if (INV) {
+#pragma unroll
+      for (int q = 1; q < R; q++) v[q] = cmul<T, true>(v[q], tw[jt * q]);
+      dftR<T, R, true>(v);
+    } else {
+      dftR<T, R, false>(v);
+#pragma unroll
+      for (int q = 1; q < R; q++) v[q] = cmul<T, false>(v[q], tw[jt * q]);
+    }
+#pragma unroll
+    for (int m = 0; m < R; m++) p[m * st] = v[m];
+  }
+}
+
+struct ZRadix {
+  int n;        // number of passes
+  int r[12];    // log2 of the radices of the forward passes in order (3, 2 or 1)
+};
+
+// S: spectrum, layout [z][ncols] (column index fastest: c = ky*nxw + kx_local).  nz = 2^m.
+template <typename T, int COLS>
+__global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensorMap tm, const Cx<T> *__restrict__ twg,
+                                                const T *__restrict__ ax, const T *__restrict__ ay,
+                                                const T *__restrict__ az, int nz, long long ncols, int nxw, int kx0,
+                                                T invN, ZRadix rad) {
+  // The tile [nz][COLS] is moved by TMA in boxes of (COLS complex) x (up to 256 rows): columns past ncols are
+  // zero-filled on load and clipped on store, and no thread spends instructions on the copy.
+  extern __shared__ unsigned char zs_raw[];
+  unsigned char *zb = zs_raw + ((128u - (smem_u32(zs_raw) & 127u)) & 127u);
+  Cx<T> *s = reinterpret_cast<Cx<T> *>(zb);       // [nz][COLS]
+  Cx<T> *tw = s + (size_t)nz * COLS;              // [nz]
+  uint64_t *bar = reinterpret_cast<uint64_t *>(tw + nz);
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const long long c0 = (long long)blockIdx.x * COLS;
+  const int ncv = (int)min((long long)COLS, ncols - c0);  // valid columns of the last tile
+  const int rows = nz < 256 ? nz : 256;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+    mbar_expect_tx(bar, (uint32_t)((size_t)nz * COLS * sizeof(Cx<T>)));
+    for (int z = 0; z < nz; z += rows) tma_load_2d(s + (size_t)z * COLS, &tm, bar, (int)(2 * c0), z);
+  }
+  for (int t = tid; t < nz; t += nt) tw[t] = twg[t];
+  __syncthreads();
+  mbar_wait(bar, 0);
+  // forward: natural -> digit-reversed
+  int lnz = 0;
+  while ((1 << lnz) < nz) lnz++;
+  int lL = lnz;  // log2 of the current block length
+  for (int p = 0; p < rad.n; p++) {
+    const int lr = rad.r[p];
+    if (lr == 3) zpass<T, 8, false, COLS>(s, tw, nz, lL - 3, tid, nt);
+    else if (lr == 2) zpass<T, 4, false, COLS>(s, tw, nz, lL - 2, tid, nt);
+    else zpass<T, 2, false, COLS>(s, tw, nz, lL - 1, tid, nt);
+    lL -= lr;
+    __syncthreads();
+  }
+  // symbol at digit-reversed positions: position pos = sum_i q_i * (nz / (R_1..R_i))  <->  kz = sum_i q_i * (R_1..R_{i-1})
+  for (int w = tid; w < nz * COLS; w += nt) {
+    const int col = w % COLS, pos = w / COLS;
+    int kz = 0, lspan = lnz, lw = 0;
+    for (int p = 0; p < rad.n; p++) {
+      lspan -= rad.r[p];
+      const int q = (pos >> lspan) & ((1 << rad.r[p]) - 1);
+      kz += q << lw;
+      lw += rad.r[p];
+    }
+    const long long c = c0 + col;
+    const int ky = (int)(c / nxw), kx = (int)(c - (long long)ky * nxw) + kx0;
+    Cx<T> v = s[w];
+    if (col < ncv) {
+      const T den = (ax[kx] + ay[ky]) + az[kz];
+      if (kx == 0 && ky == 0 && kz == 0) v = Cx<T>{T(0), T(0)};
+      else v = Cx<T>{(-v.x / den) * invN, (-v.y / den) * invN};
+      s[w] = v;
+    }
+  }
+  __syncthreads();
+  // inverse: digit-reversed -> natural (adjoint passes in reverse order)
+  for (int p = rad.n - 1; p >= 0; p--) {
+    const int lr = rad.r[p];
+    if (lr == 3) zpass<T, 8, true, COLS>(s, tw, nz, lL, tid, nt);
+    else if (lr == 2) zpass<T, 4, true, COLS>(s, tw, nz, lL, tid, nt);
+    else zpass<T, 2, true, COLS>(s, tw, nz, lL, tid, nt);
+    lL += lr;
+    __syncthreads();
+  }
+  fence_proxy_async();  // the tile written by all threads becomes visible to the bulk store
+  __syncthreads();
+  if (tid == 0) {
+    for (int z = 0; z < nz; z += rows) tma_store_2d(&tm, s + (size_t)z * COLS, (int)(2 * c0), z);
+    tma_store_commit_wait();
+  }
+}
+
+}  // namespace insb200
