@@ -23,6 +23,9 @@ in this image) and prints the line with "impl": "reference".
 import argparse
 import json
 import os
+
+# stdout carries exactly ONE JSON line: NCCL's banner ("NCCL version ...") would otherwise land on it
+os.environ["NCCL_DEBUG"] = os.environ.get("BENCH_NCCL_DEBUG", "WARN")
 import subprocess
 import sys
 import threading
@@ -340,6 +343,9 @@ def run_ours(args, wl):
     if wl["force"]:
         bf = (lambda dim, x, y, t: (dim == 1) * 5 * np.sin(np.pi * 8 * y) + 0 * x)
     setup = ins.Setup(x, Re=T(wl["Re"]), bodyforce=bf, backend=backend)
+    for kv in args.param:
+        k, v = kv.split("=")
+        setup.ctx.call("insb200_set_param", k.encode(), float(v))
     theta = wl["theta"]
     if theta is not None:
         setup.closure_model = ins.smagorinsky_closure(setup)
@@ -438,6 +444,10 @@ def run_ours(args, wl):
                    "after every step -> D2H of u; field copies amortised over K steps",
            "ke_first_last": [float(ke[0]), float(ke[-1])]}
 
+    barrier()
+    setup.ctx.close()  # collective teardown at the same program point on every rank
+    if dist is not None:
+        dist.destroy_process_group()
     if rank != 0:
         return
     # ---- CPU baseline beside it (rank 0, N = 1 only) ----------------------------------------------
@@ -473,6 +483,7 @@ def main():
     ap.add_argument("--n", type=int, default=0, help="override the per-GPU base grid size (smoke runs)")
     ap.add_argument("--cpu-n", type=int, default=None, help="grid size of the CPU baseline sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--param", action="append", default=[], help="key=value forwarded to insb200_set_param (A/B runs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours" and not args.n:
         print("bench.py: warmup < 3 is not a valid measurement; using 3", file=sys.stderr)

@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libinsb200.so")
 SOURCES = [os.path.join(CSRC, "insb200.cu")]
-HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "zsolve.cuh")] + [
     os.path.join(os.path.dirname(HERE), "include", "insb200.h")
 ]
 

@@ -115,6 +115,10 @@ struct insb200_ctx {
   void *pcplx = nullptr;                                // complex spectrum
   void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
   void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)
+  void *peerS[16] = {nullptr}, *peerB[16] = {nullptr};  // pcplx / pcplx2 of every rank mapped through CUDA IPC
+  int p2p = 0;                                          // 1: peer mappings established, transposes go over peer stores
+  int p2p_enable = 1;                                   // param "p2p": 0 forces the NCCL send/recv transpose
+  void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter
   void *ztw = nullptr;                                  // twiddles exp(-2 pi i t / n_last) of k_zsolve (complex T)
   void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)
   void *hostio = nullptr;                               // reference-layout device image for *_host calls

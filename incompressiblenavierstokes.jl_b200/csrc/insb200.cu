@@ -263,6 +263,13 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
     if (c->plan_inv_in) cufftDestroy(c->plan_inv_in);
     if (c->plan_last) cufftDestroy(c->plan_last);
   }
+  if (c->p2p) {  // unmap the peers' buffers (every rank synchronised its stream above; destroy is collective)
+    for (int q = 0; q < 16; q++) {
+      if (q != c->rank && c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
+      if (q != c->rank && c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
+    }
+  }
+  if (c->barbuf) cudaFree(c->barbuf);
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
@@ -308,6 +315,63 @@ extern "C" int insb200_local_geometry(const insb200_ctx *c, int *nloc, int *off)
 // lazily created workspaces and plans
 // =================================================================================================
 namespace insb200 {
+
+static void close_p2p(insb200_ctx *c) {
+  for (int q = 0; q < 16; q++) {
+    if (q != c->rank) {
+      if (c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
+      if (c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
+    }
+    c->peerS[q] = c->peerB[q] = nullptr;
+  }
+  c->p2p = 0;
+}
+
+// Map every rank's two spectrum buffers into this process (CUDA IPC, peer access over NVLink) so the
+// distributed-FFT transposes can store straight into the peers' memory.  Collective; on any failure on any
+// rank all ranks keep the NCCL send/recv transpose (c->p2p stays 0).
+static int setup_p2p(insb200_ctx *c) {
+  if (!c->p2p_enable || c->nranks > 16) return 0;
+  struct Rec {
+    cudaIpcMemHandle_t h[2];
+    int ok, pad[15];
+  };
+  INS_TRY(dev_alloc(c, &c->barbuf, 256));
+  std::vector<Rec> all(c->nranks);
+  Rec mine;
+  memset(&mine, 0, sizeof(mine));
+  mine.ok = cudaIpcGetMemHandle(&mine.h[0], c->pcplx) == cudaSuccess && cudaIpcGetMemHandle(&mine.h[1], c->pcplx2) == cudaSuccess;
+  if (!mine.ok) cudaGetLastError();
+  void *dev = nullptr;
+  INS_CUDA(c, cudaMalloc(&dev, sizeof(Rec) * c->nranks));
+  INS_CUDA(c, cudaMemcpyAsync((char *)dev + sizeof(Rec) * c->rank, &mine, sizeof(Rec), cudaMemcpyHostToDevice, c->stream));
+  INS_NCCL(c, ncclAllGather((char *)dev + sizeof(Rec) * c->rank, dev, sizeof(Rec), ncclChar, c->comm, c->stream));
+  INS_CUDA(c, cudaMemcpyAsync(all.data(), dev, sizeof(Rec) * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  int ok = 1;
+  for (int q = 0; q < c->nranks; q++) ok &= all[q].ok;
+  if (ok) {
+    for (int q = 0; q < c->nranks && ok; q++) {
+      if (q == c->rank) { c->peerS[q] = c->pcplx; c->peerB[q] = c->pcplx2; continue; }
+      if (cudaIpcOpenMemHandle(&c->peerS[q], all[q].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerS[q] = nullptr; ok = 0; }
+      else if (cudaIpcOpenMemHandle(&c->peerB[q], all[q].h[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerB[q] = nullptr; ok = 0; }
+    }
+    if (!ok) cudaGetLastError();
+  }
+  // agree: min over ranks
+  int *flag = (int *)c->barbuf;
+  INS_CUDA(c, cudaMemcpyAsync(flag, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  INS_NCCL(c, ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, c->comm, c->stream));
+  INS_CUDA(c, cudaMemcpyAsync(&ok, flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  INS_CUDA(c, cudaFree(dev));
+  if (!ok) {
+    close_p2p(c);
+    return 0;
+  }
+  c->p2p = 1;
+  return 0;
+}
 
 static int ensure_fft(insb200_ctx *c) {
   if (c->plans) return 0;
@@ -370,6 +434,7 @@ static int ensure_fft(insb200_ctx *c) {
       INS_CUFFT(c, cufftPlanMany(&c->plan_last, 1, nn, emb, stride, 1, emb, stride, 1, f32 ? CUFFT_C2C : CUFFT_Z2Z, stride));
       INS_CUFFT(c, cufftSetStream(c->plan_last, c->stream));
     }
+    INS_TRY(setup_p2p(c));
   }
   c->plans = true;
   return 0;
@@ -619,28 +684,45 @@ static int poisson_solve(insb200_ctx *c) {
     else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
     c->fft_execs++;
   }
-  {
-    ScopedTimer tm(c, TM_PACK);
-    k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 0);
-    CHECK_LAUNCH(c);
-  }
-  {
-    ScopedTimer tm(c, TM_A2A);
-    INS_NCCL(c, ncclGroupStart());
-    for (int q = 0; q < c->nranks; q++) {
-      const i64 ns = rows * chunk_w(q) * 2, nr = rows * c->kxl * 2;
-      if (ns) INS_NCCL(c, ncclSend((T *)(B + (i64)q * c->kxc * rows), ns, dt, q, c->comm, c->stream));
-      if (nr) INS_NCCL(c, ncclRecv((T *)(S + (i64)q * rows * c->kxl), nr, dt, q, c->comm, c->stream));
+  C *W = c->p2p ? B : S;  // the transposed spectrum (kxl fastest, ky, global z) of this rank
+  auto peer_barrier = [&]() -> int {  // all ranks' peer stores issued so far are complete and visible afterwards
+    INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
+    return 0;
+  };
+  PeerPtrs pS, pB;
+  for (int q = 0; q < 16; q++) { pS.p[q] = c->peerS[q]; pB.p[q] = c->peerB[q]; }
+  if (c->p2p) {
+    {
+      ScopedTimer tm(c, TM_PACK);
+      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, rows, c->kxc, c->rank);
+      CHECK_LAUNCH(c);
     }
-    INS_NCCL(c, ncclGroupEnd());
+    ScopedTimer tm(c, TM_A2A);
+    INS_TRY(peer_barrier());
+  } else {
+    {
+      ScopedTimer tm(c, TM_PACK);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 0);
+      CHECK_LAUNCH(c);
+    }
+    {
+      ScopedTimer tm(c, TM_A2A);
+      INS_NCCL(c, ncclGroupStart());
+      for (int q = 0; q < c->nranks; q++) {
+        const i64 ns = rows * chunk_w(q) * 2, nr = rows * c->kxl * 2;
+        if (ns) INS_NCCL(c, ncclSend((T *)(B + (i64)q * c->kxc * rows), ns, dt, q, c->comm, c->stream));
+        if (nr) INS_NCCL(c, ncclRecv((T *)(S + (i64)q * rows * c->kxl), nr, dt, q, c->comm, c->stream));
+      }
+      INS_NCCL(c, ncclGroupEnd());
+    }
   }
   if (c->kxl > 0 && D == 3 && zsolve_supported(c)) {
-    INS_TRY((launch_zsolve<T>(c, S, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
+    INS_TRY((launch_zsolve<T>(c, W, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
   } else if (c->kxl > 0) {
     {
       ScopedTimer tm(c, TM_FFT_FWD);
-      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)S, (cufftComplex *)S, CUFFT_FORWARD));
-      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)S, (cufftDoubleComplex *)S, CUFFT_FORWARD));
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)W, (cufftComplex *)W, CUFFT_FORWARD));
+      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)W, (cufftDoubleComplex *)W, CUFFT_FORWARD));
       c->fft_execs++;
     }
     {
@@ -648,31 +730,42 @@ static int poisson_solve(insb200_ctx *c) {
       // layout (kxl fastest, ky, kz) in 3-D; (kxl fastest, ky) in 2-D
       const int nky = c->nglob[1], nkz = D == 3 ? c->nglob[2] : 1;
       dim3 blk(64, 4, 1), grd((c->kxl + 63) / 64, (nky + 3) / 4, nkz);
-      k_poisson_scale<T, C, D><<<grd, blk, 0, c->stream>>>(S, (const T *)c->ahat[0], (const T *)c->ahat[1], (const T *)c->ahat[2],
+      k_poisson_scale<T, C, D><<<grd, blk, 0, c->stream>>>(W, (const T *)c->ahat[0], (const T *)c->ahat[1], (const T *)c->ahat[2],
                                                          c->kxl, nky, nkz, c->kx0, invN);
       CHECK_LAUNCH(c);
     }
     {
       ScopedTimer tm(c, TM_FFT_INV);
-      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)S, (cufftComplex *)S, CUFFT_INVERSE));
-      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)S, (cufftDoubleComplex *)S, CUFFT_INVERSE));
+      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2C(c->plan_last, (cufftComplex *)W, (cufftComplex *)W, CUFFT_INVERSE));
+      else INS_CUFFT(c, cufftExecZ2Z(c->plan_last, (cufftDoubleComplex *)W, (cufftDoubleComplex *)W, CUFFT_INVERSE));
       c->fft_execs++;
     }
   }
-  {
-    ScopedTimer tm(c, TM_A2A);
-    INS_NCCL(c, ncclGroupStart());
-    for (int q = 0; q < c->nranks; q++) {
-      const i64 ns = rows * c->kxl * 2, nr = rows * chunk_w(q) * 2;
-      if (ns) INS_NCCL(c, ncclSend((T *)(S + (i64)q * rows * c->kxl), ns, dt, q, c->comm, c->stream));
-      if (nr) INS_NCCL(c, ncclRecv((T *)(B + (i64)q * c->kxc * rows), nr, dt, q, c->comm, c->stream));
+  if (c->p2p) {
+    if (c->kxl > 0) {
+      ScopedTimer tm(c, TM_PACK);
+      const unsigned grd = (unsigned)((rows * c->nranks + 4 * kScatterRows - 1) / (4 * kScatterRows));
+      k_fft_scatter_bwd<C><<<grd, pblk, 0, c->stream>>>(pS, W, c->nxh, rows, c->kxl, c->kx0, c->nranks);
+      CHECK_LAUNCH(c);
     }
-    INS_NCCL(c, ncclGroupEnd());
-  }
-  {
-    ScopedTimer tm(c, TM_PACK);
-    k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 1);
-    CHECK_LAUNCH(c);
+    ScopedTimer tm(c, TM_A2A);
+    INS_TRY(peer_barrier());
+  } else {
+    {
+      ScopedTimer tm(c, TM_A2A);
+      INS_NCCL(c, ncclGroupStart());
+      for (int q = 0; q < c->nranks; q++) {
+        const i64 ns = rows * c->kxl * 2, nr = rows * chunk_w(q) * 2;
+        if (ns) INS_NCCL(c, ncclSend((T *)(S + (i64)q * rows * c->kxl), ns, dt, q, c->comm, c->stream));
+        if (nr) INS_NCCL(c, ncclRecv((T *)(B + (i64)q * c->kxc * rows), nr, dt, q, c->comm, c->stream));
+      }
+      INS_NCCL(c, ncclGroupEnd());
+    }
+    {
+      ScopedTimer tm(c, TM_PACK);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 1);
+      CHECK_LAUNCH(c);
+    }
   }
   {
     ScopedTimer tm(c, TM_FFT_INV);
@@ -1515,6 +1608,10 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "zchunk") { if (v < 2) INS_FAIL(c, "zchunk must be >= 2"); c->zchunk = v; }
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
+  else if (k == "p2p") {
+    if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
+    c->p2p_enable = v != 0;
+  }
   else if (k == "zcols") { if (v != 0 && v != 4 && v != 8 && v != 16) INS_FAIL(c, "zcols must be 0, 4, 8 or 16"); c->zcols = v; }
   else if (k == "zthreads") { if (v < 64 || v > 512 || v % 32) INS_FAIL(c, "zthreads must be a multiple of 32 in [64, 512]"); c->zthreads = v; }
   else INS_FAIL(c, "unknown parameter: " + k);

@@ -50,6 +50,8 @@ def main():
         bf = kolmogorov(D) if force else None
         so = o.Setup(x, Re=T(800), bodyforce=bf)
         sc = ins.Setup(x, Re=T(800), bodyforce=bf, backend=backend)
+        if "MGPU_P2P" in os.environ:  # A/B: 0 = NCCL send/recv transposes, 1 = peer-memory scatter
+            sc.ctx.call("insb200_set_param", b"p2p", float(os.environ["MGPU_P2P"]))
         if theta is not None:
             so.closure_model = o.smagorinsky_closure(so)
             sc.closure_model = ins.smagorinsky_closure(sc)
