@@ -81,6 +81,8 @@ struct insb200_ctx {
   int rank = 0, nranks = 1;
   int variant = 2;         // 0: one thread per cell, 1: LDG-tiled stage kernel, 2: TMA plane pipeline (3-D)
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
+  int smag_v = 2;          // closure kernel: 1 = shared-memory stencil (k_smag3d_tma), 2 = register-carried (k_smag3d_v2)
+  int smag_zchunk = 128;   // planes marched per block of k_smag3d_v2
   int zchunk = 64;         // tiled stage kernel: planes marched per block
   int padded = 0;          // 1: padded layout with real ghost cells (3-D)
   int org[3] = {0, 0, 0};  // interior origin inside the padded box (elements)

@@ -1194,6 +1194,21 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 4, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 5, &tp));
+  if constexpr (sizeof(T) == 4) if (c->smag_v >= 2) {  // register-carried z-march, one block of TX x (TY+4) threads per SM (F32)
+    typedef Smag2Cfg<T, PG, kTX, kTY> Cfg2;
+    auto kern2 = k_smag3d_v2<T, PG, kTX, kTY>;
+    static bool attr2_set = false;
+    if (!attr2_set) {
+      INS_CUDA(c, cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM));
+      attr2_set = true;
+    }
+    const int zc2 = std::max(2, std::min(c->smag_zchunk, c->nloc[2]));
+    dim3 grd2(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc2 - 1) / zc2), blk2(kTX, kTY + 4, 1);
+    kern2<<<grd2, blk2, Cfg2::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc2, c->org[0], c->org[1],
+                                              c->org[2]);
+    CHECK_LAUNCH(c);
+    return 0;
+  }
   auto kern = k_smag3d_tma<T, PG, kTX, kTY>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -1608,6 +1623,8 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "zchunk") { if (v < 2) INS_FAIL(c, "zchunk must be >= 2"); c->zchunk = v; }
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
+  else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
+  else if (k == "smag_zchunk") { if (v < 2) INS_FAIL(c, "smag_zchunk must be >= 2"); c->smag_zchunk = v; }
   else if (k == "p2p") {
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
     c->p2p_enable = v != 0;

@@ -64,14 +64,14 @@ __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarr
 // NS+1 pressure slots because the prologue holds planes 0..NS at once.  All shared-memory addressing is
 // by element offset from one base pointer, and the slot offsets are rotated in registers (no modulo in
 // the plane loop).
-template <typename T, int TX, int BYU, bool PGRAD, int NS_>
+template <typename T, int TX, int BYU, bool PGRAD, int NS_, int NPS_ = NS_ + 1>
 struct PlanePipe {
   static constexpr int NS = NS_;
   static constexpr int V = 16 / (int)sizeof(T);   // elements per 16 B
   static constexpr int XL = V;                    // left x margin of the box (>= 2 halo cells)
   static constexpr int BX = TX + 2 * V;           // box width: i0-XL .. i0+TX+V-1
   static constexpr int BYP = BYU + 1;
-  static constexpr int NPS = NS + 1;
+  static constexpr int NPS = NPS_;
   static constexpr int UPL = BYU * BX;            // elements of one component plane
   static constexpr int USLOT = ((3 * UPL * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
   static constexpr int PSLOT = ((BYP * BX * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
@@ -492,6 +492,215 @@ __global__ void __launch_bounds__(TX *TY, (sizeof(T) == 4 ? 2 : 1))
     pa = pb;
     pb = pb + PSLOT == PEND ? POFF : pb + PSLOT;
     o += sz;
+  }
+}
+
+// -------------------------------------------------------------------------------------------------
+// k_smag3d_v2: the same operator with the z-march carried in REGISTERS.  Every thread keeps the part of
+// its stencil that lies on the lower planes from the iterations before (13 velocity values per p-cell,
+// 11 tensor values per u-cell), so per plane a p-cell reads 17 instead of 30 velocity words and a u-cell
+// 19 instead of 30 tensor words from shared memory -- the v1 kernel is bound by shared-memory wavefronts
+// and issue slots, not by HBM.  One block of TX x (TY+4) threads per SM: thread l < (TX+2)(TY+2) owns
+// p-cell l of the sigma tile (no second pass), threads with ty < TY own a u-cell.  The loop is skewed so
+// that ONE barrier per plane suffices: iteration `it` projects velocity plane it+3, forms sigma(it) from
+// the velocity planes it+1 (registers + mid extras) and it+2 (top), and takes the divergence of sigma
+// planes it-3 .. it-1 for the output plane z = kbeg + it - 3; the three parts touch disjoint memory.
+// Arithmetic is smag_sigma / divsigma_comp unchanged (register-backed accessors): bit-identical to v1.
+// -------------------------------------------------------------------------------------------------
+// Register files of the march.  Planes rotate through three register sets; PH (= iteration mod 3, a
+// compile-time constant of the unrolled loop) says which set is bottom / mid / top, so that advancing one
+// plane moves no data.
+template <typename T>
+struct RegU {
+  T x[3][2], xe[4];  // ux: {0, -x} per plane set; mid-plane extras {+y, +y-x, -y, -y-x}
+  T y[3][2], ye[4];  // uy: {0, -y} per plane set; mid-plane extras {+x, +x-y, -x, -x-y}
+  T z[3][5];         // uz: {0, +x, -x, +y, -y} per plane set (mid and bottom are live)
+};
+template <typename T, int PH>
+struct RegUView {  // dz = -1, 0, +1 -> set (PH + dz + 1) % 3
+  const RegU<T> &r;
+  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
+    const int s = (PH + dz + 1) % 3;
+    if (c == 0) return dy == 0 ? r.x[s][-dx] : r.xe[(dy > 0 ? 0 : 2) - dx];
+    if (c == 1) return dx == 0 ? r.y[s][-dy] : r.ye[(dx > 0 ? 0 : 2) - dy];
+    return r.z[s][dx > 0 ? 1 : (dx < 0 ? 2 : (dy > 0 ? 3 : (dy < 0 ? 4 : 0)))];
+  }
+};
+
+template <typename T>
+struct RegSg {
+  T xx[2], yy[2], zz[3];  // {0, +x}, {0, +y}; sigma_zz(0) per plane set (mid and top are live)
+  T xy[8];                // (0,0) (1,0) (0,1) (1,1) (0,-1) (1,-1) (-1,0) (-1,1)
+  T xz[3][3], yz[3][3];   // sigma_xz {0, +x, -x}, sigma_yz {0, +y, -y} per plane set
+};
+template <typename T, int PH>
+struct RegSgView {
+  const RegSg<T> &r;
+  __device__ __forceinline__ T operator()(int c, int dx, int dy, int dz) const {
+    const int s = (PH + dz + 1) % 3;
+    if (c == 0) return r.xx[dx];
+    if (c == 3) return r.yy[dy];
+    if (c == 5) return r.zz[s];
+    if (c == 1) return r.xy[dy == 0 ? (dx == 0 ? 0 : (dx > 0 ? 1 : 6)) : (dy > 0 ? (dx == 0 ? 2 : (dx > 0 ? 3 : 7)) : (dx == 0 ? 4 : 5))];
+    if (c == 2) return r.xz[s][dx == 0 ? 0 : (dx > 0 ? 1 : 2)];
+    return r.yz[s][dy == 0 ? 0 : (dy > 0 ? 1 : 2)];
+  }
+};
+
+template <int J>
+struct IntC {
+  static constexpr int value = J;
+};
+
+template <typename T, bool PGRAD, int TX, int TY>
+struct Smag2Cfg {
+  typedef PlanePipe<T, TX, TY + 4, PGRAD, 6, 6> Pipe;  // 6 velocity and 6 pressure slots: period of the unrolled loop
+  static constexpr int NT = TX * (TY + 4);
+  static constexpr int SX = TX + 2, SY = TY + 2, SPL = SX * SY, SSLOT = 6 * SPL;
+  static_assert(SPL <= NT, "one p-cell of the sigma tile per thread");
+  static constexpr size_t SMEM = 128 + (size_t)(Pipe::ELEMS + 3 * SSLOT) * sizeof(T) + 8 * Pipe::NS + 16;
+};
+
+template <typename T, bool PGRAD, int TX, int TY>
+__global__ void __launch_bounds__(TX *(TY + 4), 1)
+    k_smag3d_v2(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p, T *__restrict__ sout,
+                i64 sy_, i64 sz_, i64 sc_, Geo g, T c_eddy, Rh<T> rh, int zc, int ox, int oy, int oz) {
+  typedef Smag2Cfg<T, PGRAD, TX, TY> Cfg;
+  typedef typename Cfg::Pipe Pipe;
+  constexpr int BX = Pipe::BX, UPL = Pipe::UPL, NT = Cfg::NT, XL = Pipe::XL, NS = Pipe::NS, USLOT = Pipe::USLOT;
+  constexpr int POFF = Pipe::POFF, PSLOT = Pipe::PSLOT;
+  constexpr int SX = Cfg::SX, SPL = Cfg::SPL, SSLOT = Cfg::SSLOT;
+  constexpr int SOFF = Pipe::ELEMS;  // sigma ring follows the plane slots
+  static_assert(NS == 6 && Pipe::NPS == 6, "slot periods must divide the unroll factor");
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char *sb = smem_raw + ((128u - (smem_u32(smem_raw) & 127u)) & 127u);
+  T *su = reinterpret_cast<T *>(sb);
+  uint64_t *bars = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(su + SOFF + 3 * SSLOT) + 7) & ~(uintptr_t)7);
+
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * TX + tx;
+  const int i0 = blockIdx.x * TX, j0 = blockIdx.y * TY;
+  const int kbeg = blockIdx.z * zc, nk = min(zc, g.n[2] - kbeg);
+  const unsigned sz = (unsigned)sz_, sc = (unsigned)sc_;
+
+  Pipe pipe;
+  pipe.init(su, bars, &tm_u, &tm_p, ox + i0 - XL, oy + j0 - 2, oz + kbeg - 2, tid);
+  __syncthreads();
+  const int qlast = nk + 3;  // velocity planes q = 0 .. nk+3 <-> z = kbeg-2 .. kbeg+nk+1
+  if (tid == 0) {
+#pragma unroll
+    for (int q = 0; q < NS - 1; q++)  // the pressure ring holds planes 0 .. NS-1 at this point
+      if (q <= qlast) pipe.issue(q);
+  }
+  pipe.wait(0);
+  pipe.project_q(0, tid, NT, rh.v);
+  __syncthreads();
+
+  const bool sig_thr = tid < SPL, div_thr = ty < TY;
+  const int ly = tid / SX, lx = tid - ly * SX;
+  const int cu = sig_thr ? (ly + 1) * BX + lx - 1 + XL : BX + XL;  // p-cell (lx-1, ly-1); box row 0 is y = -2
+  const int c_sig = (ty + 1) * SX + tx + 1;
+  unsigned o = (unsigned)kbeg * sz + (unsigned)(j0 + ty) * (unsigned)sy_ + i0 + tx;
+
+  RegU<T> U;
+  RegSg<T> Sg;
+#pragma unroll
+  for (int s = 0; s < 3; s++) {
+    U.x[s][0] = U.x[s][1] = U.y[s][0] = U.y[s][1] = Sg.zz[s] = T(0);
+#pragma unroll
+    for (int i = 0; i < 5; i++) U.z[s][i] = T(0);
+#pragma unroll
+    for (int i = 0; i < 3; i++) Sg.xz[s][i] = Sg.yz[s][i] = T(0);
+  }
+
+  // One plane step; J = (it + 2) mod 6 is a compile-time constant, so every slot offset below is an
+  // immediate: velocity plane q lives in slot q mod 6, pressure plane q in slot q mod 6, sigma plane r in
+  // ring slot (r + 2) mod 3.
+  auto step = [&](auto jc, const int it, const unsigned par) {
+    constexpr int J = decltype(jc)::value, PH = J % 3;
+    constexpr int u_mid = ((J + 5) % 6) * USLOT, u_top = (J % 6) * USLOT, u_prj = ((J + 1) % 6) * USLOT;
+    constexpr int pa = POFF + ((J + 1) % 6) * PSLOT, pb = POFF + ((J + 2) % 6) * PSLOT;
+    constexpr int g_w = SOFF + PH * SSLOT, g_t = SOFF + ((PH + 2) % 3) * SSLOT, g_m = SOFF + ((PH + 1) % 3) * SSLOT;
+    constexpr int TOP = (PH + 2) % 3, MID = (PH + 1) % 3;
+    // ---- A: velocity plane it+3 lands and is projected in place
+    if (it + 3 <= qlast) {
+      pipe.wait_slot((J + 1) % 6, J == 5 ? par ^ 1u : par);
+      pipe.project(u_prj, pa, pb, tid, NT, rh.v);
+    }
+    // ---- B: sigma(it) at this thread's p-cell
+    if (sig_thr && it <= nk + 1) {
+      const T *ut = su + u_top + cu;
+      U.x[TOP][0] = ut[0];
+      U.x[TOP][1] = ut[-1];
+      U.y[TOP][0] = ut[UPL];
+      U.y[TOP][1] = ut[UPL - BX];
+      if (it >= -1) {
+        const T *um = su + u_mid + cu;
+        U.xe[0] = um[BX];
+        U.xe[1] = um[BX - 1];
+        U.xe[2] = um[-BX];
+        U.xe[3] = um[-BX - 1];
+        U.ye[0] = um[UPL + 1];
+        U.ye[1] = um[UPL + 1 - BX];
+        U.ye[2] = um[UPL - 1];
+        U.ye[3] = um[UPL - 1 - BX];
+        U.z[MID][0] = um[2 * UPL];
+        U.z[MID][1] = um[2 * UPL + 1];
+        U.z[MID][2] = um[2 * UPL - 1];
+        U.z[MID][3] = um[2 * UPL + BX];
+        U.z[MID][4] = um[2 * UPL - BX];
+        if (it >= 0) {
+          T sig[6];
+          RegUView<T, PH> Uv{U};
+          smag_sigma<T, 3>(Uv, c_eddy, rh.v, sig);
+#pragma unroll
+          for (int c = 0; c < 6; c++) su[g_w + c * SPL + tid] = sig[c];
+        }
+      }
+    }
+    // ---- C: s(z = kbeg + it - 3) = div sigma from sigma planes it-3 (registers), it-2, it-1
+    if (div_thr && it >= 1) {
+      const T *st = su + g_t + c_sig;
+      Sg.xz[TOP][0] = st[2 * SPL];
+      Sg.xz[TOP][1] = st[2 * SPL + 1];
+      Sg.xz[TOP][2] = st[2 * SPL - 1];
+      Sg.yz[TOP][0] = st[4 * SPL];
+      Sg.yz[TOP][1] = st[4 * SPL + SX];
+      Sg.yz[TOP][2] = st[4 * SPL - SX];
+      Sg.zz[TOP] = st[5 * SPL];
+      if (it >= 3) {
+        const T *sm = su + g_m + c_sig;
+        Sg.xx[0] = sm[0];
+        Sg.xx[1] = sm[1];
+        Sg.yy[0] = sm[3 * SPL];
+        Sg.yy[1] = sm[3 * SPL + SX];
+        Sg.xy[0] = sm[SPL];
+        Sg.xy[1] = sm[SPL + 1];
+        Sg.xy[2] = sm[SPL + SX];
+        Sg.xy[3] = sm[SPL + SX + 1];
+        Sg.xy[4] = sm[SPL - SX];
+        Sg.xy[5] = sm[SPL - SX + 1];
+        Sg.xy[6] = sm[SPL - 1];
+        Sg.xy[7] = sm[SPL + SX - 1];
+        RegSgView<T, PH> Sv{Sg};
+#pragma unroll
+        for (int a = 0; a < 3; a++) sout[o + a * sc] = divsigma_comp<T, 3>(Sv, a, rh.v);
+        o += sz;
+      }
+    }
+    __syncthreads();
+    // velocity plane it+1 is retired: its slot takes plane it+1+NS
+    if (tid == 0 && it + 1 + NS <= qlast) pipe.issue(it + 1 + NS);
+  };
+
+  unsigned par = 0;  // phase parity of the barriers of planes 6m+1 .. 6m+5 (plane 6m+6 has the opposite one)
+  for (int it = -2; it <= nk + 2; it += 6) {
+    step(IntC<0>{}, it, par);
+    if (it + 1 <= nk + 2) step(IntC<1>{}, it + 1, par);
+    if (it + 2 <= nk + 2) step(IntC<2>{}, it + 2, par);
+    if (it + 3 <= nk + 2) step(IntC<3>{}, it + 3, par);
+    if (it + 4 <= nk + 2) step(IntC<4>{}, it + 4, par);
+    if (it + 5 <= nk + 2) step(IntC<5>{}, it + 5, par);
+    par ^= 1u;
   }
 }
 

@@ -225,7 +225,11 @@ def test_kernel_variants_bit_identical(T, smag):
                          ("tiled16_zc7_nofuse", dict(variant=1, tile_y=16, zchunk=7, fuse_gradient=0)),
                          ("tma_zc64", dict(variant=2, zchunk=64)),
                          ("tma_zc7", dict(variant=2, zchunk=7)),
-                         ("tma_zc2", dict(variant=2, zchunk=2))]:
+                         ("tma_zc2", dict(variant=2, zchunk=2)),
+                         ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1)),
+                         ("tma_smag_v2_zc128", dict(variant=2, smag_v=2, smag_zchunk=128)),
+                         ("tma_smag_v2_zc7", dict(variant=2, smag_v=2, smag_zchunk=7)),
+                         ("tma_smag_v2_zc2", dict(variant=2, smag_v=2, smag_zchunk=2))]:
         for k, v in params.items():
             set_param(sc, k, v)
         u = ins.to_device(u0, sc)
