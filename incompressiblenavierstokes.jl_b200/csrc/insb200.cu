@@ -560,7 +560,7 @@ static bool zsolve_supported(const insb200_ctx *c) {
 template <typename T, int COLS>
 static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad) {
   const int nz = c->nglob[2];
-  const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + 16;
+  const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + (size_t)nz * sizeof(T) + 16;
   auto kern = k_zsolve<T, COLS>;
   // 2-D descriptor of the spectrum seen as [nz][2*ncols] words of T, box = (2*COLS) x min(nz, 256)
   CUtensorMap tm;
@@ -591,7 +591,7 @@ static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0,
   }
   const unsigned nb = (unsigned)((ncols + COLS - 1) / COLS);
   kern<<<nb, c->zthreads, smem, c->stream>>>(tm, (const Cx<T> *)c->ztw, (const T *)c->ahat[0], (const T *)c->ahat[1],
-                                     (const T *)c->ahat[2], nz, ncols, nxw, kx0, invN, rad);
+                                     (const T *)c->ahat[2], nz, ncols, nxw, kx0, T(-1) / invN, rad);
   CHECK_LAUNCH(c);
   return 0;
 }

@@ -114,6 +114,38 @@ __device__ __forceinline__ void zpass(Cx<T> *s, const Cx<T> *tw, int nz, int lsu
   }
 }
 
+template <typename T> __device__ __forceinline__ T rcp_(T x) { return T(1) / x; }
+template <> __device__ __forceinline__ float rcp_<float>(float x) { return __frcp_rn(x); }
+
+// The last forward pass (sub-stride 1: its twiddles are all 1), the symbol and the first inverse pass touch the
+// same R consecutive positions of a column: one trip through registers.  Position b*R+q holds the mode
+// kz = digitrev(b*R+q), whose az is tabulated in azr; the scaling is v * 1/(((ax+ay)+az) * (-N)).
+// `axy`, `zero_col` belong to the thread's column, which does not change over the loop (nt % COLS == 0).
+template <typename T, int R, int COLS>
+__device__ __forceinline__ void zpass_mid(Cx<T> *s, const T *azr, int nz, int tid, int nt, T axy, T negN, bool zero_col) {
+  constexpr int LR = R == 8 ? 3 : (R == 4 ? 2 : 1), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
+  const int nw = (nz >> LR) << LC;
+#pragma unroll 2
+  for (int w = tid; w < nw; w += nt) {
+    const int col = w & (COLS - 1), b = w >> LC;
+    Cx<T> *p = s + ((b << LR) << LC) + col;
+    Cx<T> v[R];
+#pragma unroll
+    for (int m = 0; m < R; m++) v[m] = p[m * COLS];
+    dftR<T, R, false>(v);
+    const T *a = azr + (b << LR);
+#pragma unroll
+    for (int q = 0; q < R; q++) {
+      T r = rcp_<T>(((axy + a[q])) * negN);
+      if (q == 0 && zero_col && b == 0) r = T(0);  // the constant mode
+      v[q] = Cx<T>{v[q].x * r, v[q].y * r};
+    }
+    dftR<T, R, true>(v);
+#pragma unroll
+    for (int m = 0; m < R; m++) p[m * COLS] = v[m];
+  }
+}
+
 struct ZRadix {
   int n;        // number of passes
   int r[12];    // log2 of the radices of the forward passes in order (3, 2 or 1)
@@ -124,17 +156,17 @@ template <typename T, int COLS>
 __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensorMap tm, const Cx<T> *__restrict__ twg,
                                                 const T *__restrict__ ax, const T *__restrict__ ay,
                                                 const T *__restrict__ az, int nz, long long ncols, int nxw, int kx0,
-                                                T invN, ZRadix rad) {
+                                                T negN, ZRadix rad) {
   // The tile [nz][COLS] is moved by TMA in boxes of (COLS complex) x (up to 256 rows): columns past ncols are
   // zero-filled on load and clipped on store, and no thread spends instructions on the copy.
   extern __shared__ unsigned char zs_raw[];
   unsigned char *zb = zs_raw + ((128u - (smem_u32(zs_raw) & 127u)) & 127u);
   Cx<T> *s = reinterpret_cast<Cx<T> *>(zb);       // [nz][COLS]
   Cx<T> *tw = s + (size_t)nz * COLS;              // [nz]
-  uint64_t *bar = reinterpret_cast<uint64_t *>(tw + nz);
+  T *azr = reinterpret_cast<T *>(tw + nz);        // [nz]  az at digit-reversed positions
+  uint64_t *bar = reinterpret_cast<uint64_t *>(azr + nz);
   const int tid = threadIdx.x, nt = blockDim.x;
   const long long c0 = (long long)blockIdx.x * COLS;
-  const int ncv = (int)min((long long)COLS, ncols - c0);  // valid columns of the last tile
   const int rows = nz < 256 ? nz : 256;
   if (tid == 0) {
     mbar_init(bar, 1);
@@ -142,14 +174,29 @@ __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensor
     mbar_expect_tx(bar, (uint32_t)((size_t)nz * COLS * sizeof(Cx<T>)));
     for (int z = 0; z < nz; z += rows) tma_load_2d(s + (size_t)z * COLS, &tm, bar, (int)(2 * c0), z);
   }
-  for (int t = tid; t < nz; t += nt) tw[t] = twg[t];
-  __syncthreads();
-  mbar_wait(bar, 0);
-  // forward: natural -> digit-reversed
   int lnz = 0;
   while ((1 << lnz) < nz) lnz++;
+  for (int t = tid; t < nz; t += nt) {
+    tw[t] = twg[t];
+    // position t = sum_i q_i * (nz / (R_1..R_i))  <->  kz = sum_i q_i * (R_1..R_{i-1})
+    int kz = 0, lspan = lnz, lw = 0;
+    for (int p = 0; p < rad.n; p++) {
+      lspan -= rad.r[p];
+      kz += ((t >> lspan) & ((1 << rad.r[p]) - 1)) << lw;
+      lw += rad.r[p];
+    }
+    azr[t] = az[kz];
+  }
+  // this thread's column (columns past ncols are zero-filled by the load and clipped by the store)
+  const long long c = min(c0 + (tid & (COLS - 1)), ncols - 1);
+  const int ky = (int)(c / nxw), kx = (int)(c - (long long)ky * nxw) + kx0;
+  const T axy = ax[kx] + ay[ky];
+  const bool zero_col = kx == 0 && ky == 0;
+  __syncthreads();
+  mbar_wait(bar, 0);
+  // forward: natural -> digit-reversed; all passes but the last
   int lL = lnz;  // log2 of the current block length
-  for (int p = 0; p < rad.n; p++) {
+  for (int p = 0; p + 1 < rad.n; p++) {
     const int lr = rad.r[p];
     if (lr == 3) zpass<T, 8, false, COLS>(s, tw, nz, lL - 3, tid, nt);
     else if (lr == 2) zpass<T, 4, false, COLS>(s, tw, nz, lL - 2, tid, nt);
@@ -157,29 +204,15 @@ __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensor
     lL -= lr;
     __syncthreads();
   }
-  // symbol at digit-reversed positions: position pos = sum_i q_i * (nz / (R_1..R_i))  <->  kz = sum_i q_i * (R_1..R_{i-1})
-  for (int w = tid; w < nz * COLS; w += nt) {
-    const int col = w % COLS, pos = w / COLS;
-    int kz = 0, lspan = lnz, lw = 0;
-    for (int p = 0; p < rad.n; p++) {
-      lspan -= rad.r[p];
-      const int q = (pos >> lspan) & ((1 << rad.r[p]) - 1);
-      kz += q << lw;
-      lw += rad.r[p];
-    }
-    const long long c = c0 + col;
-    const int ky = (int)(c / nxw), kx = (int)(c - (long long)ky * nxw) + kx0;
-    Cx<T> v = s[w];
-    if (col < ncv) {
-      const T den = (ax[kx] + ay[ky]) + az[kz];
-      if (kx == 0 && ky == 0 && kz == 0) v = Cx<T>{T(0), T(0)};
-      else v = Cx<T>{(-v.x / den) * invN, (-v.y / den) * invN};
-      s[w] = v;
-    }
+  {
+    const int lr = rad.r[rad.n - 1];  // == lL
+    if (lr == 3) zpass_mid<T, 8, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
+    else if (lr == 2) zpass_mid<T, 4, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
+    else zpass_mid<T, 2, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
+    __syncthreads();
   }
-  __syncthreads();
   // inverse: digit-reversed -> natural (adjoint passes in reverse order)
-  for (int p = rad.n - 1; p >= 0; p--) {
+  for (int p = rad.n - 2; p >= 0; p--) {
     const int lr = rad.r[p];
     if (lr == 3) zpass<T, 8, true, COLS>(s, tw, nz, lL, tid, nt);
     else if (lr == 2) zpass<T, 4, true, COLS>(s, tw, nz, lL, tid, nt);
