@@ -889,6 +889,11 @@ static int op_scalewithvolume(insb200_ctx *c, void *p) {
 template <typename T, int D, int MODE>
 static int launch_gradient(insb200_ctx *c, View<T> out, View<const T> p, Geo gp) {
   ScopedTimer tm(c, TM_GRADIENT);
+  if constexpr (D == 3) {
+    constexpr int ZPT = 4;
+    dim3 grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 3) / 4, (c->nloc[2] + ZPT - 1) / ZPT);
+    k_gradient_z<T, MODE, ZPT><<<grd, cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
+  } else
   k_gradient<T, D, MODE><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
   CHECK_LAUNCH(c);
   return 0;

@@ -346,6 +346,57 @@ __global__ void k_gradient(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
   }
 }
 
+// 3-D form marching ZPT planes per thread: p(k+1) of one plane is p(k) of the next (one load less per
+// cell), the x / y wrap is resolved once, and the grid has ZPT times fewer blocks.
+template <typename T, int MODE, int ZPT>
+__global__ void k_gradient_z(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k0 = blockIdx.z * ZPT;
+  if (i >= gp.n[0] || j >= gp.n[1]) return;
+  int ip = i + 1, jp = j + 1;
+  if (gp.wrap[0] && ip >= gp.n[0]) ip -= gp.n[0];
+  if (gp.wrap[1] && jp >= gp.n[1]) jp -= gp.n[1];
+  const i64 pc = (i64)j * p.sy + i, px = (i64)j * p.sy + ip, py = (i64)jp * p.sy + i;
+  const int nk = min(ZPT, gp.n[2] - k0);
+  T pz[ZPT + 1], pxv[ZPT], pyv[ZPT];
+#pragma unroll
+  for (int m = 0; m <= ZPT; m++) {
+    int kk = k0 + m;
+    if (gp.wrap[2] && kk >= gp.n[2]) kk -= gp.n[2];
+    if (m <= nk) pz[m] = __ldg(p.p + (i64)kk * p.sz + pc);
+    if (m < nk) {
+      pxv[m] = __ldg(p.p + (i64)kk * p.sz + px);
+      pyv[m] = __ldg(p.p + (i64)kk * p.sz + py);
+    }
+  }
+  T *o = out.p + (i64)k0 * out.sz + (i64)j * out.sy + i;
+  if (MODE == 0) {
+#pragma unroll
+    for (int m = 0; m < ZPT; m++)
+      if (m < nk) {
+        o[m * out.sz] = (pxv[m] - pz[m]) * rh.v[0];
+        o[m * out.sz + out.sc] = (pyv[m] - pz[m]) * rh.v[1];
+        o[m * out.sz + 2 * out.sc] = (pz[m + 1] - pz[m]) * rh.v[2];
+      }
+  } else {
+    T u[ZPT][3];
+#pragma unroll
+    for (int m = 0; m < ZPT; m++)
+      if (m < nk) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) u[m][a] = o[m * out.sz + a * out.sc];
+      }
+#pragma unroll
+    for (int m = 0; m < ZPT; m++)
+      if (m < nk) {
+        o[m * out.sz] = u[m][0] - (pxv[m] - pz[m]) * rh.v[0];
+        o[m * out.sz + out.sc] = u[m][1] - (pyv[m] - pz[m]) * rh.v[1];
+        o[m * out.sz + 2 * out.sc] = u[m][2] - (pz[m + 1] - pz[m]) * rh.v[2];
+      }
+  }
+}
+
 // whole-array scale (scalewithvolume! on the reference layout, ghosts included)
 template <typename T>
 __global__ void k_scale(T *p, i64 n, T f) {
