@@ -237,7 +237,7 @@ def cpu_sample(wl, steps=1, n=None):
 
 # words (sizeof(T)) per cell per LAUNCH of each library kernel: the algorithmic minimum, every
 # logical field read / written once (DESIGN.md "Kernels and rooflines")
-def kernel_words(D, smag, force, nstages=4, tma=False):
+def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False):
     """Algorithmic words per cell per LAUNCH of each library kernel (every logical field read / written once)."""
     ntens = D * (D + 1) // 2
     extra = (D if force else 0)
@@ -263,14 +263,21 @@ def kernel_words(D, smag, force, nstages=4, tma=False):
         w["momentum_stage_last"] = 3.0 * D + 2 + D * (nstages - 1) + extra + sadd
         # R u, R p (all but the first stage), W s; sigma never leaves shared memory
         w["smagorinsky_fused"] = 2.0 * D + (nstages - 1.0) / nstages
+    if zsolve:
+        # k_zsolve does the last-axis transforms and the symbol in one read + write of the half spectrum
+        # ("poisson_scale" timer); cuFFT only transforms the D-1 in-plane axes
+        w["cufft_forward"] = w["cufft_inverse"] = 2.0 * (D - 1)
     return w
 
 
 # DRAM bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum) of one `ncu --set full` capture at the
-# default workload size; see profiles/r1_ncu_full_tma_kernels.txt
+# default workload size; see profiles/r1_ncu_full_kernels_v3.txt
 NCU_TRAFFIC = {
-    ("dt3d_smag", 512, "smagorinsky_fused"): 2.524938e9 + 1.580448e9,
-    ("dt3d_smag", 512, "momentum_stage"): 5.969720e9 + 3.732034e9,
+    ("dt3d_smag", 512, "smagorinsky_fused"): 2.450518e9 + 1.580941e9,
+    ("dt3d_smag", 512, "momentum_stage"): 5.952208e9 + 3.730599e9,
+    ("dt3d_smag", 512, "momentum_stage_last"): 11.164976e9 + 2.139155e9,
+    ("dt3d_smag", 512, "poisson_scale"): 0.539117e9 + 0.502182e9,
+    ("dt3d_smag", 512, "pressure_gradient"): 2.283003e9 + 1.561083e9,
 }
 
 
@@ -405,7 +412,9 @@ def run_ours(args, wl):
     setup.ctx.call("insb200_set_profiling", 0)
     esz = np.dtype(T).itemsize
     cells_local = cells / world
-    words = kernel_words(D, theta is not None, wl["force"], tma=(D == 3 and base_n % 32 == 0))
+    nz_glob = n[-1]
+    words = kernel_words(D, theta is not None, wl["force"], tma=(D == 3 and base_n % 32 == 0),
+                         zsolve=(D == 3 and 8 <= nz_glob <= 2048 and nz_glob & (nz_glob - 1) == 0))
     peak, peak_src = peaks()
     kern = {}
     for name, (tms, cnt) in timers.items():
