@@ -27,7 +27,7 @@ __all__ = [
     "diffusion", "convectiondiffusion", "divergence_", "divergence", "scalewithvolume_",
     "pressuregradient_", "pressuregradient", "applypressure_", "applypressure", "psolver_spectral",
     "default_psolver", "poisson_", "poisson", "project_", "project", "pressure_", "pressure",
-    "smagorinsky_closure", "total_kinetic_energy", "get_cfl_timestep_", "maxabs", "RKMethods",
+    "smagorinsky_closure", "total_kinetic_energy", "get_cfl_timestep_", "maxabs", "RKMethods", "LMWray3",
     "runge_kutta_method", "ode_method_cache", "create_stepper", "timestep_", "solve_unsteady",
     "solve_unsteady_host", "init_distributed", "local_slab", "gather_slabs",
 ]
@@ -455,31 +455,92 @@ def runge_kutta_method(A, b, c, r, T=np.float64, **kw):
     return ExplicitRungeKuttaMethod(A, b.astype(T), c, T(r), **kw)
 
 
-class RKMethods:
-    """The explicit tableaux of src/time_steppers/RKMethods.jl that the examples use; any other
-    explicit tableau can be passed through `runge_kutta_method`."""
+def _rowsum(A):
+    return np.sum(np.array(A, dtype=np.float64), axis=1)
 
-    @staticmethod
-    def FE11(**kw):  # RKMethods.jl: forward Euler
-        return runge_kutta_method([[0]], [1], [0], 1, **kw)
 
-    @staticmethod
-    def SSP22(**kw):
-        return runge_kutta_method([[0, 0], [1, 0]], [1 / 2, 1 / 2], [0, 1], 1, **kw)
+_S6 = float(np.sqrt(6.0))
+# name -> (A, b, c or None (= row sums of A), r): the explicit tableaux of src/time_steppers/RKMethods.jl
+# (file:line of each constructor in the comments).  Fractions are written as Python floats (Float64).
+_EXPLICIT_TABLEAUX = {
+    "FE11": ([[0]], [1], [0], 1),                                                                          # :45-51
+    "SSP22": ([[0, 0], [1, 0]], [1 / 2, 1 / 2], None, 1),                                                  # :54-60
+    "SSP42": ([[0, 0, 0, 0], [1 / 3, 0, 0, 0], [1 / 3, 1 / 3, 0, 0], [1 / 3, 1 / 3, 1 / 3, 0]], [1 / 4] * 4, None, 3),  # :63-70
+    "SSP33": ([[0, 0, 0], [1, 0, 0], [1 / 4, 1 / 4, 0]], [1 / 6, 1 / 6, 2 / 3], None, 1),                  # :73-79
+    "SSP43": ([[0, 0, 0, 0], [1 / 2, 0, 0, 0], [1 / 2, 1 / 2, 0, 0], [1 / 6, 1 / 6, 1 / 6, 0]], [1 / 6, 1 / 6, 1 / 6, 1 / 2], None, 2),  # :82-88
+    "Wray3": ([[0, 0, 0], [8 / 15, 0, 0], [8 / 15 - 17 / 60, 5 / 12, 0]], [8 / 15 - 17 / 60, 0, 3 / 4],
+              [0, 8 / 15, 8 / 15 - 17 / 60 + 5 / 12], 0),                                                  # :137-146
+    "RK56": ([[0, 0, 0, 0, 0, 0], [1 / 4, 0, 0, 0, 0, 0], [1 / 8, 1 / 8, 0, 0, 0, 0], [0, 0, 1 / 2, 0, 0, 0],
+              [3 / 16, -3 / 8, 3 / 8, 9 / 16, 0, 0], [-3 / 7, 8 / 7, 6 / 7, -12 / 7, 8 / 7, 0]],
+             [7 / 90, 0, 16 / 45, 2 / 15, 16 / 45, 7 / 90], [0, 1 / 4, 1 / 4, 1 / 2, 3 / 4, 1], 0),         # :149-162
+    "DOPRI6": ([[0, 0, 0, 0, 0, 0], [1 / 5, 0, 0, 0, 0, 0], [3 / 40, 9 / 40, 0, 0, 0, 0], [44 / 45, -56 / 15, 32 / 9, 0, 0, 0],
+                [19372 / 6561, -25360 / 2187, 64448 / 6561, -212 / 729, 0, 0],
+                [9017 / 3168, -355 / 33, 46732 / 5247, 49 / 176, -5103 / 18656, 0]],
+               [35 / 384, 0, 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84], None, 0),                      # :165-178
+    "HEM3": ([[0, 0, 0], [1 / 3, 0, 0], [-1, 2, 0]], [0, 3 / 4, 1 / 4], None, 0),                           # :235-241
+    "HEM3BS": ([[0, 0, 0], [1 / 2, 0, 0], [-1, 2, 0]], [1 / 6, 2 / 3, 1 / 6], None, 0),                     # :244-250
+    "HEM5": ([[0, 0, 0, 0, 0], [3 / 10, 0, 0, 0, 0], [(1 + _S6) / 30, (11 - 4 * _S6) / 30, 0, 0, 0],
+              [(-79 - 31 * _S6) / 150, (-1 - 4 * _S6) / 30, (24 + 11 * _S6) / 25, 0, 0],
+              [(14 + 5 * _S6) / 6, (-8 + 7 * _S6) / 6, (-9 - 7 * _S6) / 4, (9 - _S6) / 4, 0]],
+             [0, 0, (16 - _S6) / 36, (16 + _S6) / 36, 1 / 9], None, 0),                                    # :253-265
+    "Mid22": ([[0, 0], [1 / 2, 0]], [0, 1], [0, 1 / 2], 1 / 2),                                            # :461-467
+    "MTE22": ([[0, 0], [2 / 3, 0]], [1 / 4, 3 / 4], [0, 2 / 3], 1 / 2),                                    # :470-476
+    "Heun33": ([[0, 0, 0], [1 / 3, 0, 0], [0, 2 / 3, 0]], [1 / 4, 0, 3 / 4], None, 0),                      # :488-494
+    "RK33C2": ([[0, 0, 0], [2 / 3, 0, 0], [1 / 3, 1 / 3, 0]], [1 / 4, 0, 3 / 4], [0, 2 / 3, 2 / 3], 0),     # :497-503
+    "RK33P2": ([[0, 0, 0], [1 / 3, 0, 0], [-1, 2, 0]], [0, 3 / 4, 1 / 4], [0, 1 / 3, 1], 0),                # :506-512
+    "RK44": ([[0, 0, 0, 0], [1 / 2, 0, 0, 0], [0, 1 / 2, 0, 0], [0, 0, 1, 0]], [1 / 6, 1 / 3, 1 / 3, 1 / 6], None, 0),  # :515-521
+    "RK44C2": ([[0, 0, 0, 0], [1 / 4, 0, 0, 0], [0, 1 / 2, 0, 0], [1, -2, 2, 0]], [1 / 6, 0, 2 / 3, 1 / 6], [0, 1 / 4, 1 / 2, 1], 0),  # :524-530
+    "RK44C23": ([[0, 0, 0, 0], [1 / 2, 0, 0, 0], [1 / 4, 1 / 4, 0, 0], [0, -1, 2, 0]], [1 / 6, 0, 2 / 3, 1 / 6], [0, 1 / 2, 1 / 2, 1], 0),  # :533-539
+    "RK44P2": ([[0, 0, 0, 0], [1, 0, 0, 0], [3 / 8, 1 / 8, 0, 0], [-1 / 8, -3 / 8, 3 / 2, 0]], [1 / 6, -1 / 18, 2 / 3, 2 / 9], [0, 1, 1 / 2, 1], 0),  # :542-548
+    "NSSP21": ([[0, 0], [3 / 4, 0]], [0, 1], [0, 3 / 4], 0),                                               # :589-598
+    "NSSP32": ([[0, 0, 0], [1 / 3, 0, 0], [0, 1, 0]], [1 / 2, 0, 1 / 2], [0, 1 / 3, 1], 0),                 # :601-611
+    "NSSP33": ([[0, 0, 0], [-4 / 9, 0, 0], [7 / 6, -1 / 2, 0]], [1 / 4, 0, 3 / 4], [0, -4 / 9, 2 / 3], 0),  # :614-624
+    "NSSP53": ([[0, 0, 0, 0, 0], [1 / 7, 0, 0, 0, 0], [0, 3 / 16, 0, 0, 0], [0, 0, 1 / 3, 0, 0], [0, 0, 0, 2 / 3, 0]],
+               [1 / 4, 0, 0, 0, 3 / 4], [0, 1 / 7, 3 / 16, 1 / 3, 2 / 3], 0),                               # :627-641
+}
 
-    @staticmethod
-    def RK33P2(**kw):  # RKMethods.jl:505-511
-        return runge_kutta_method([[0, 0, 0], [1 / 3, 0, 0], [-1, 2, 0]], [0, 3 / 4, 1 / 4], [0, 1 / 3, 1], 0, **kw)
 
-    @staticmethod
-    def RK44(**kw):  # RKMethods.jl:515-521
-        A = [[0, 0, 0, 0], [1 / 2, 0, 0, 0], [0, 1 / 2, 0, 0], [0, 0, 1, 0]]
-        return runge_kutta_method(A, [1 / 6, 1 / 3, 1 / 3, 1 / 6], np.sum(np.array(A), axis=1), 0, **kw)
+class _RKMethods:
+    """RKMethods.<name>(T=...) for every EXPLICIT tableau of src/time_steppers/RKMethods.jl:45-641 (the
+    implicit, DSRK and the matrix-generated SSP104 / rSSPs families are outside the explicit stepper);
+    any other explicit tableau goes through `runge_kutta_method(A, b, c, r)`."""
 
-    @staticmethod
-    def RK44C2(**kw):  # RKMethods.jl:524-530
-        A = [[0, 0, 0, 0], [1 / 4, 0, 0, 0], [0, 1 / 2, 0, 0], [1, -2, 2, 0]]
-        return runge_kutta_method(A, [1 / 6, 0, 2 / 3, 1 / 6], np.sum(np.array(A), axis=1), 0, **kw)
+    names = tuple(_EXPLICIT_TABLEAUX)
+
+    def __getattr__(self, name):
+        if name not in _EXPLICIT_TABLEAUX:
+            raise AttributeError(f"RKMethods has no explicit tableau {name!r}")
+        A, b, c, r = _EXPLICIT_TABLEAUX[name]
+
+        def make(**kw):
+            return runge_kutta_method(A, b, _rowsum(A) if c is None else c, r, **kw)
+
+        make.__name__ = name
+        return make
+
+
+RKMethods = _RKMethods()
+
+
+class LMWray3:
+    """LMWray3{T}  src/time_steppers/methods.jl (low-storage Wray RK3) with the step of
+    step_lmwray3.jl:4-104: per stage  k = f(u);  u = project(xstart + dt*a_i*k);  xstart += dt*b_i*k.
+    Unrolled, stage i is  u_i = x0 + dt*(b_1 k_1 + .. + b_{i-1} k_{i-1} + a_i k_i)  added in that order, i.e.
+    the explicit stage combination (step_explicit_runge_kutta.jl:35-38) with the shifted tableau below -- same
+    operations in the same order, so the library runs it through `insb200_rk_step`; it keeps u, xstart and the
+    k_j with a non-zero b_j (k_1 only) instead of six vector fields."""
+
+    a = (8 / 15, 5 / 12, 3 / 4)
+    b = (1 / 4, 0.0)
+    c_stage = (0.0, 8 / 15, 2 / 3)
+
+    def __init__(self, T=np.float64):
+        a, b = self.a, self.b
+        self.A = np.array([[a[0], 0, 0], [b[0], a[1], 0], [b[0], b[1], a[2]]], dtype=np.float64).astype(T)
+        self.b = self.A[-1].copy()
+        # time level reached after each stage's projection; the step ends at t + dt (step_lmwray3.jl:97)
+        self.c = np.array([self.c_stage[1], self.c_stage[2], 1.0], dtype=np.float64).astype(T)
+        self.r = T(0)
 
 
 def ode_method_cache(method, setup):

@@ -82,6 +82,7 @@ struct insb200_ctx {
   int variant = 2;         // 0: one thread per cell, 1: LDG-tiled stage kernel, 2: TMA plane pipeline (3-D)
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
   int smag_v = 2;          // closure kernel: 1 = shared-memory stencil (k_smag3d_tma), 2 = register-carried (k_smag3d_v2)
+  int smag_ty = 16;        // tile height of k_smag3d_v2: 16 (one 640-thread block per SM) or 8 (two 384-thread blocks)
   int smag_zchunk = 128;   // planes marched per block of k_smag3d_v2
   int zchunk = 64;         // tiled stage kernel: planes marched per block
   int padded = 0;          // 1: padded layout with real ghost cells (3-D)
@@ -118,6 +119,9 @@ struct insb200_ctx {
   void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
   void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)
   void *peerS[16] = {nullptr}, *peerB[16] = {nullptr};  // pcplx / pcplx2 of every rank mapped through CUDA IPC
+  std::map<int, std::vector<CUtensorMap>> peer_tmaps;   // k_zsolve_peer descriptors of the peers' spectra, key = COLS*64 + CX
+  int p2p_fused = 0;                                    // param "p2p_fused": k_zsolve_peer gathers / scatters the spectrum itself (3-D, needs p2p)
+  int nxp = 0;                                          // row pitch (complex words) of the in-slab spectrum, >= nxh
   int p2p = 0;                                          // 1: peer mappings established, transposes go over peer stores
   int p2p_enable = 1;                                   // param "p2p": 0 forces the NCCL send/recv transpose
   void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter

@@ -228,6 +228,8 @@ extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype,
   }
   c->nxh = n[0] / 2 + 1;
   c->kxc = (c->nxh + nranks - 1) / nranks;
+  if (nranks > 1 && dtype == INSB200_F32) c->kxc = (c->kxc + 1) & ~1;  // 16-B aligned chunk starts (TMA on the peers' spectra)
+  c->nxp = c->nxh;
   c->kx0 = std::min(rank * c->kxc, c->nxh);
   c->kxl = std::min((rank + 1) * c->kxc, c->nxh) - c->kx0;
 
@@ -409,14 +411,16 @@ static int ensure_fft(insb200_ctx *c) {
   } else {
     // rows of the in-slab spectrum: 3-D: ny*nzl, 2-D: nyl
     const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
-    const i64 slots = (i64)c->nranks * c->kxc * rows;  // >= rows*nxh and >= nranks*rows*kxl
+    // row pitch of the in-slab spectrum: a multiple of 16 B so that the peers can address it by TMA
+    if (D == 3 && f32) c->nxp = (c->nxh + 1) & ~1;
+    const i64 slots = std::max((i64)c->nranks * c->kxc, (i64)c->nxp) * rows;  // >= rows*nxp and >= nranks*rows*kxl
     INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
     INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
     if (D == 3) {
       int nn[2] = {c->nloc[1], c->nloc[0]};
       int remb[2] = {c->ext[1], c->ext[0]};
-      int cemb[2] = {c->nloc[1], c->nxh};
-      const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxh;
+      int cemb[2] = {c->nloc[1], c->nxp};
+      const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxp;
       INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
       INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
     } else {
@@ -596,10 +600,9 @@ static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0,
   return 0;
 }
 
-// S: [z][ncols] spectrum with all nz points of the last axis local; columns c = ky*nxw + (kx - kx0)
+// twiddle table exp(-2 pi i t / nz) (Float64 on the host, stored in T) and the radix plan of the last axis
 template <typename T>
-static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN) {
-  ScopedTimer tm(c, TM_POISSON_SCALE);
+static int zsolve_prepare(insb200_ctx *c, ZRadix &rad) {
   const int nz = c->nglob[2];
   if (!c->ztw) {
     std::vector<Cx<T>> tw(nz);
@@ -611,18 +614,94 @@ static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T
     INS_CUDA(c, cudaMemcpyAsync(c->ztw, tw.data(), nz * sizeof(Cx<T>), cudaMemcpyHostToDevice, c->stream));
     INS_CUDA(c, cudaStreamSynchronize(c->stream));
   }
-  ZRadix rad;
   rad.n = 0;
   int m = 0;
   while ((1 << m) < nz) m++;
   while (m >= 3) { rad.r[rad.n++] = 3; m -= 3; }  // log2 of the radix: 8, 8, .. then 4 or 2
   if (m > 0) rad.r[rad.n++] = m;
+  return 0;
+}
+
+// S: [z][ncols] spectrum with all nz points of the last axis local; columns c = ky*nxw + (kx - kx0)
+template <typename T>
+static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN) {
+  ScopedTimer tm(c, TM_POISSON_SCALE);
+  const int nz = c->nglob[2];
+  ZRadix rad;
+  INS_TRY((zsolve_prepare<T>(c, rad)));
   const size_t col_bytes = (size_t)nz * sizeof(Cx<T>);
   if (c->zcols == 4) return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
   if (c->zcols == 8 && 8 * col_bytes <= 131072) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
   if (16 * col_bytes <= 65536) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);
   if (8 * col_bytes <= 65536) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
   return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
+}
+
+// fused transposes + last-axis solve over the peers' in-slab spectra (k_zsolve_peer)
+template <typename T, int COLS>
+static int launch_zsolve_peer_i(insb200_ctx *c, T invN, const ZRadix &rad, bool local_load) {
+  const int nz = c->nglob[2], nzl = c->nloc[2], ny = c->nglob[1], P = c->nranks;
+  // columns of a tile: CX consecutive kx times CY = COLS/CX consecutive ky; least padding of the kx range wins
+  int CX = COLS;
+  for (int cx = COLS; cx * (int)sizeof(Cx<T>) >= 32; cx >>= 1) {
+    const int pad = (c->kxl + cx - 1) / cx * cx, best = (c->kxl + CX - 1) / CX * CX;
+    if (pad < best) CX = cx;
+  }
+  const int CY = COLS / CX;
+  int lcx = 0;
+  while ((1 << lcx) < CX) lcx++;
+  const int key = COLS * 64 + CX;
+  auto it = c->peer_tmaps.find(key);
+  if (it == c->peer_tmaps.end()) {
+    void *fn = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    INS_CUDA(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+    if (!fn || qr != cudaDriverEntryPointSuccess) INS_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
+    std::vector<CUtensorMap> maps(P + 1);  // [P]: the local transposed copy pcplx2 = [nz][ny][kxl, pitch kxp]
+    const int kxp = sizeof(T) == 4 ? (c->kxl + 1) & ~1 : c->kxl;
+    for (int q = 0; q <= P; q++) {
+      void *base = q < P ? (void *)((char *)c->peerS[q] + (size_t)c->kx0 * sizeof(Cx<T>)) : c->pcplx2;
+      const int pitch = q < P ? c->nxp : kxp;
+      cuuint64_t dims[3] = {(cuuint64_t)(2 * c->kxl), (cuuint64_t)ny, (cuuint64_t)(q < P ? nzl : nz)};
+      cuuint64_t strides[2] = {(cuuint64_t)pitch * sizeof(Cx<T>), (cuuint64_t)pitch * ny * sizeof(Cx<T>)};
+      cuuint32_t box[3] = {(cuuint32_t)(2 * CX), (cuuint32_t)CY, (cuuint32_t)std::min(nzl, 256)};
+      cuuint32_t estr[3] = {1, 1, 1};
+      CUresult r = ((PFN_tmap_encode)fn)(&maps[q], sizeof(T) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3,
+                                         base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      if (r != CUDA_SUCCESS) INS_FAIL(c, "cuTensorMapEncodeTiled (peer spectrum) failed with CUresult " + std::to_string((int)r));
+    }
+    it = c->peer_tmaps.emplace(key, std::move(maps)).first;
+  }
+  PeerMaps pm;
+  memset(&pm, 0, sizeof(pm));
+  for (int q = 0; q < P; q++) pm.m[q] = it->second[q];
+  const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + (size_t)nz * sizeof(T) + 16;
+  auto kern = k_zsolve_peer<T, COLS>;
+  static size_t attr = 0;
+  if (smem > attr) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  const int tiles_x = (c->kxl + CX - 1) / CX, tiles_y = (ny + CY - 1) / CY;
+  kern<<<(unsigned)(tiles_x * tiles_y), c->zthreads, smem, c->stream>>>(pm, it->second[P], local_load ? 1 : 0, (const Cx<T> *)c->ztw, (const T *)c->ahat[0],
+                                                                      (const T *)c->ahat[1], (const T *)c->ahat[2], nz, nzl, P, lcx,
+                                                                      tiles_x, c->kxl, c->kx0, ny, T(-1) / invN, rad);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T>
+static int launch_zsolve_peer(insb200_ctx *c, T invN, bool local_load) {
+  ScopedTimer tm(c, TM_POISSON_SCALE);
+  ZRadix rad;
+  INS_TRY((zsolve_prepare<T>(c, rad)));
+  const size_t col_bytes = (size_t)c->nglob[2] * sizeof(Cx<T>);
+  if (c->zcols == 4) return launch_zsolve_peer_i<T, 4>(c, invN, rad, local_load);
+  if (c->zcols == 8 && 8 * col_bytes <= 131072) return launch_zsolve_peer_i<T, 8>(c, invN, rad, local_load);
+  if (16 * col_bytes <= 65536) return launch_zsolve_peer_i<T, 16>(c, invN, rad, local_load);
+  if (8 * col_bytes <= 65536) return launch_zsolve_peer_i<T, 8>(c, invN, rad, local_load);
+  return launch_zsolve_peer_i<T, 4>(c, invN, rad, local_load);
 }
 
 // ---- spectral Poisson solve on the compact real buffer (in: preal interior = rhs; out: solution) --
@@ -691,10 +770,28 @@ static int poisson_solve(insb200_ctx *c) {
   };
   PeerPtrs pS, pB;
   for (int q = 0; q < 16; q++) { pS.p[q] = c->peerS[q]; pB.p[q] = c->peerB[q]; }
+  if (c->p2p && c->p2p_fused && D == 3 && zsolve_supported(c) && c->nranks <= 8) {
+    // p2p_fused = 2: every rank gathers its kx range of the peers' spectra inside the solve kernel (peer loads);
+    // p2p_fused = 1: the way there is k_fft_scatter_fwd (peer stores), only the way back is fused into the solve
+    const bool local_load = c->p2p_fused == 1;
+    if (local_load) {
+      ScopedTimer tm(c, TM_PACK);
+      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, sizeof(T) == 4);
+      CHECK_LAUNCH(c);
+    }
+    { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all in-slab transforms / forward scatters are complete
+    if (c->kxl > 0) INS_TRY((launch_zsolve_peer<T>(c, invN, local_load)));
+    { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all peers' stores into this rank's spectrum are complete
+    ScopedTimer tm(c, TM_FFT_INV);
+    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
+    else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
+    c->fft_execs++;
+    return 0;
+  }
   if (c->p2p) {
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, rows, c->kxc, c->rank);
+      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, 0);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
@@ -702,7 +799,7 @@ static int poisson_solve(insb200_ctx *c) {
   } else {
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 0);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, 0);
       CHECK_LAUNCH(c);
     }
     {
@@ -745,7 +842,7 @@ static int poisson_solve(insb200_ctx *c) {
     if (c->kxl > 0) {
       ScopedTimer tm(c, TM_PACK);
       const unsigned grd = (unsigned)((rows * c->nranks + 4 * kScatterRows - 1) / (4 * kScatterRows));
-      k_fft_scatter_bwd<C><<<grd, pblk, 0, c->stream>>>(pS, W, c->nxh, rows, c->kxl, c->kx0, c->nranks);
+      k_fft_scatter_bwd<C><<<grd, pblk, 0, c->stream>>>(pS, W, c->nxp, rows, c->kxl, c->kx0, c->nranks);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
@@ -763,7 +860,7 @@ static int poisson_solve(insb200_ctx *c) {
     }
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, rows, c->kxc, 1);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, 1);
       CHECK_LAUNCH(c);
     }
   }
@@ -1199,7 +1296,26 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 4, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 5, &tp));
-  if constexpr (sizeof(T) == 4) if (c->smag_v >= 2) {  // register-carried z-march, one block of TX x (TY+4) threads per SM (F32)
+  if constexpr (sizeof(T) == 4) if (c->smag_v >= 2) {  // register-carried z-march (F32)
+    const int zc2 = std::max(2, std::min(c->smag_zchunk, c->nloc[2]));
+    if (c->smag_ty == 8 && c->nloc[1] % 8 == 0) {  // two blocks of 32 x 12 threads per SM
+      typedef Smag2Cfg<T, PG, kTX, 8> Cfg2;
+      CUtensorMap tu8, tp8;
+      INS_TRY(get_tmap(c, ubase, 3, Cfg2::Pipe::BX, 8 + 4, &tu8));
+      INS_TRY(get_tmap(c, pbase, 1, Cfg2::Pipe::BX, 8 + 5, &tp8));
+      auto kern2 = k_smag3d_v2<T, PG, kTX, 8>;
+      static bool attr8_set = false;
+      if (!attr8_set) {
+        INS_CUDA(c, cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM));
+        attr8_set = true;
+      }
+      dim3 grd2(c->nloc[0] / kTX, c->nloc[1] / 8, (c->nloc[2] + zc2 - 1) / zc2), blk2(kTX, 8 + 4, 1);
+      kern2<<<grd2, blk2, Cfg2::SMEM, c->stream>>>(tu8, tp8, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc2, c->org[0],
+                                                c->org[1], c->org[2]);
+      CHECK_LAUNCH(c);
+      return 0;
+    }
+    // one block of 32 x 20 threads per SM
     typedef Smag2Cfg<T, PG, kTX, kTY> Cfg2;
     auto kern2 = k_smag3d_v2<T, PG, kTX, kTY>;
     static bool attr2_set = false;
@@ -1207,7 +1323,6 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
       INS_CUDA(c, cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM));
       attr2_set = true;
     }
-    const int zc2 = std::max(2, std::min(c->smag_zchunk, c->nloc[2]));
     dim3 grd2(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc2 - 1) / zc2), blk2(kTX, kTY + 4, 1);
     kern2<<<grd2, blk2, Cfg2::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc2, c->org[0], c->org[1],
                                               c->org[2]);
@@ -1629,7 +1744,9 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
   else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
+  else if (k == "smag_ty") { if (v != 8 && v != 16) INS_FAIL(c, "smag_ty must be 8 or 16"); c->smag_ty = v; }
   else if (k == "smag_zchunk") { if (v < 2) INS_FAIL(c, "smag_zchunk must be >= 2"); c->smag_zchunk = v; }
+  else if (k == "p2p_fused") { if (v < 0 || v > 2) INS_FAIL(c, "p2p_fused must be 0, 1 or 2"); c->p2p_fused = v; }
   else if (k == "p2p") {
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
     c->p2p_enable = v != 0;

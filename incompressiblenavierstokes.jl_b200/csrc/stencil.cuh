@@ -511,8 +511,8 @@ __global__ void k_reduce_final(const double *part_ke, const double *part_max, i6
 // unpack is the inverse of pack on the way back.
 // ---------------------------------------------------------------------------------------------
 template <typename C>
-__global__ void k_fft_pack(C *B, const C *__restrict__ S, int nxh, i64 rows /* ny*nzl (or nyl in 2-D) */, int kxc,
-                           int dir /*0: S->B, 1: B->S*/) {
+__global__ void k_fft_pack(C *B, const C *__restrict__ S, int nxh, int ps /* row pitch of S */, i64 rows /* ny*nzl (or nyl in 2-D) */,
+                           int kxc, int dir /*0: S->B, 1: B->S*/) {
   const int i = blockIdx.y * blockDim.x + threadIdx.x;                  // kx
   const i64 r = (i64)blockIdx.x * blockDim.y + threadIdx.y;              // row
   if (i >= nxh || r >= rows) return;
@@ -520,8 +520,8 @@ __global__ void k_fft_pack(C *B, const C *__restrict__ S, int nxh, i64 rows /* n
   const int kq = i - q * kxc;
   const int w = min(kxc, nxh - q * kxc);  // width of q's chunk
   const i64 bo = (i64)q * kxc * rows + r * w + kq;
-  if (dir == 0) B[bo] = S[r * nxh + i];
-  else ((C *)S)[r * nxh + i] = B[bo];
+  if (dir == 0) B[bo] = S[r * ps + i];
+  else ((C *)S)[r * ps + i] = B[bo];
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -542,17 +542,18 @@ struct PeerPtrs {
 constexpr int kScatterRows = 4;
 
 template <typename C>
-__global__ void k_fft_scatter_fwd(PeerPtrs W, const C *__restrict__ S, int nxh, i64 rows, int kxc, int rank) {
+__global__ void k_fft_scatter_fwd(PeerPtrs W, const C *__restrict__ S, int nxh, int ps, i64 rows, int kxc, int rank, int even) {
   const i64 r0 = ((i64)blockIdx.x * blockDim.y + threadIdx.y) * kScatterRows;
   for (int i = threadIdx.x; i < nxh; i += blockDim.x) {  // kx
     const int q = i / kxc;
     const int kq = i - q * kxc;
-    const int w = min(kxc, nxh - q * kxc);  // width of q's chunk
+    int w = min(kxc, nxh - q * kxc);  // width of q's chunk
+    if (even) w = (w + 1) & ~1;            // row pitch of W_q rounded to 16 B (read by TMA)
     C *dst = reinterpret_cast<C *>(W.p[q]) + ((i64)rank * rows + r0) * w + kq;
     C v[kScatterRows];
 #pragma unroll
     for (int j = 0; j < kScatterRows; j++)
-      if (r0 + j < rows) v[j] = S[(r0 + j) * nxh + i];
+      if (r0 + j < rows) v[j] = S[(r0 + j) * ps + i];
 #pragma unroll
     for (int j = 0; j < kScatterRows; j++)
       if (r0 + j < rows) dst[(i64)j * w] = v[j];
@@ -560,7 +561,7 @@ __global__ void k_fft_scatter_fwd(PeerPtrs W, const C *__restrict__ S, int nxh, 
 }
 
 template <typename C>
-__global__ void k_fft_scatter_bwd(PeerPtrs S, const C *__restrict__ W, int nxh, i64 rows, int kxl, int kx0, int nranks) {
+__global__ void k_fft_scatter_bwd(PeerPtrs S, const C *__restrict__ W, int ps, i64 rows, int kxl, int kx0, int nranks) {
   const i64 R0 = ((i64)blockIdx.x * blockDim.y + threadIdx.y) * kScatterRows;  // global row = q*rows + row
   const i64 tot = rows * nranks;
   C *dst[kScatterRows];
@@ -568,7 +569,7 @@ __global__ void k_fft_scatter_bwd(PeerPtrs S, const C *__restrict__ W, int nxh, 
   for (int j = 0; j < kScatterRows; j++) {
     const i64 R = min(R0 + j, tot - 1);
     const int q = (int)(R / rows);
-    dst[j] = reinterpret_cast<C *>(S.p[q]) + (R - (i64)q * rows) * nxh + kx0;
+    dst[j] = reinterpret_cast<C *>(S.p[q]) + (R - (i64)q * rows) * ps + kx0;
   }
   for (int k = threadIdx.x; k < kxl; k += blockDim.x) {  // local kx
     C v[kScatterRows];

@@ -562,7 +562,7 @@ struct Smag2Cfg {
 };
 
 template <typename T, bool PGRAD, int TX, int TY>
-__global__ void __launch_bounds__(TX *(TY + 4), 1)
+__global__ void __launch_bounds__(TX *(TY + 4), (TY <= 8 ? 2 : 1))
     k_smag3d_v2(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p, T *__restrict__ sout,
                 i64 sy_, i64 sz_, i64 sc_, Geo g, T c_eddy, Rh<T> rh, int zc, int ox, int oy, int oz) {
   typedef Smag2Cfg<T, PGRAD, TX, TY> Cfg;

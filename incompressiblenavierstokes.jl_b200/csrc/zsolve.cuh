@@ -28,6 +28,17 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, const void *
                "r"(x), "r"(y), "r"(smem_u32(src))
                : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *tm, uint64_t *bar, int x, int y, int z) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                   smem_u32(dst)),
+               "l"(reinterpret_cast<uint64_t>(tm)), "r"(x), "r"(y), "r"(z), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap *tm, const void *src, int x, int y, int z) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(reinterpret_cast<uint64_t>(tm)),
+               "r"(x), "r"(y), "r"(z), "r"(smem_u32(src))
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_commit_wait() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -151,31 +162,10 @@ struct ZRadix {
   int r[12];    // log2 of the radices of the forward passes in order (3, 2 or 1)
 };
 
-// S: spectrum, layout [z][ncols] (column index fastest: c = ky*nxw + kx_local).  nz = 2^m.
-template <typename T, int COLS>
-__global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensorMap tm, const Cx<T> *__restrict__ twg,
-                                                const T *__restrict__ ax, const T *__restrict__ ay,
-                                                const T *__restrict__ az, int nz, long long ncols, int nxw, int kx0,
-                                                T negN, ZRadix rad) {
-  // The tile [nz][COLS] is moved by TMA in boxes of (COLS complex) x (up to 256 rows): columns past ncols are
-  // zero-filled on load and clipped on store, and no thread spends instructions on the copy.
-  extern __shared__ unsigned char zs_raw[];
-  unsigned char *zb = zs_raw + ((128u - (smem_u32(zs_raw) & 127u)) & 127u);
-  Cx<T> *s = reinterpret_cast<Cx<T> *>(zb);       // [nz][COLS]
-  Cx<T> *tw = s + (size_t)nz * COLS;              // [nz]
-  T *azr = reinterpret_cast<T *>(tw + nz);        // [nz]  az at digit-reversed positions
-  uint64_t *bar = reinterpret_cast<uint64_t *>(azr + nz);
-  const int tid = threadIdx.x, nt = blockDim.x;
-  const long long c0 = (long long)blockIdx.x * COLS;
-  const int rows = nz < 256 ? nz : 256;
-  if (tid == 0) {
-    mbar_init(bar, 1);
-    fence_barrier_init();
-    mbar_expect_tx(bar, (uint32_t)((size_t)nz * COLS * sizeof(Cx<T>)));
-    for (int z = 0; z < nz; z += rows) tma_load_2d(s + (size_t)z * COLS, &tm, bar, (int)(2 * c0), z);
-  }
-  int lnz = 0;
-  while ((1 << lnz) < nz) lnz++;
+// twiddles and az-at-digit-reversed-positions tables of a block (all threads; followed by a barrier at the caller)
+template <typename T>
+__device__ __forceinline__ void zsolve_tables(Cx<T> *tw, T *azr, const Cx<T> *__restrict__ twg, const T *__restrict__ az, int nz,
+                                              int lnz, const ZRadix &rad, int tid, int nt) {
   for (int t = tid; t < nz; t += nt) {
     tw[t] = twg[t];
     // position t = sum_i q_i * (nz / (R_1..R_i))  <->  kz = sum_i q_i * (R_1..R_{i-1})
@@ -187,13 +177,12 @@ __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensor
     }
     azr[t] = az[kz];
   }
-  // this thread's column (columns past ncols are zero-filled by the load and clipped by the store)
-  const long long c = min(c0 + (tid & (COLS - 1)), ncols - 1);
-  const int ky = (int)(c / nxw), kx = (int)(c - (long long)ky * nxw) + kx0;
-  const T axy = ax[kx] + ay[ky];
-  const bool zero_col = kx == 0 && ky == 0;
-  __syncthreads();
-  mbar_wait(bar, 0);
+}
+
+// forward passes, symbol, inverse passes on the resident tile s[nz][COLS]; ends with a barrier
+template <typename T, int COLS>
+__device__ __forceinline__ void zsolve_tile(Cx<T> *s, const Cx<T> *tw, const T *azr, int nz, int lnz, const ZRadix &rad, int tid,
+                                            int nt, T axy, T negN, bool zero_col) {
   // forward: natural -> digit-reversed; all passes but the last
   int lL = lnz;  // log2 of the current block length
   for (int p = 0; p + 1 < rad.n; p++) {
@@ -220,10 +209,109 @@ __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensor
     lL += lr;
     __syncthreads();
   }
+}
+
+// S: spectrum, layout [z][ncols] (column index fastest: c = ky*nxw + kx_local).  nz = 2^m.
+template <typename T, int COLS>
+__global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensorMap tm, const Cx<T> *__restrict__ twg,
+                                                const T *__restrict__ ax, const T *__restrict__ ay,
+                                                const T *__restrict__ az, int nz, long long ncols, int nxw, int kx0,
+                                                T negN, ZRadix rad) {
+  // The tile [nz][COLS] is moved by TMA in boxes of (COLS complex) x (up to 256 rows): columns past ncols are
+  // zero-filled on load and clipped on store, and no thread spends instructions on the copy.
+  extern __shared__ unsigned char zs_raw[];
+  unsigned char *zb = zs_raw + ((128u - (smem_u32(zs_raw) & 127u)) & 127u);
+  Cx<T> *s = reinterpret_cast<Cx<T> *>(zb);       // [nz][COLS]
+  Cx<T> *tw = s + (size_t)nz * COLS;              // [nz]
+  T *azr = reinterpret_cast<T *>(tw + nz);        // [nz]  az at digit-reversed positions
+  uint64_t *bar = reinterpret_cast<uint64_t *>(azr + nz);
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const long long c0 = (long long)blockIdx.x * COLS;
+  const int rows = nz < 256 ? nz : 256;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+    mbar_expect_tx(bar, (uint32_t)((size_t)nz * COLS * sizeof(Cx<T>)));
+    for (int z = 0; z < nz; z += rows) tma_load_2d(s + (size_t)z * COLS, &tm, bar, (int)(2 * c0), z);
+  }
+  int lnz = 0;
+  while ((1 << lnz) < nz) lnz++;
+  zsolve_tables<T>(tw, azr, twg, az, nz, lnz, rad, tid, nt);
+  // this thread's column (columns past ncols are zero-filled by the load and clipped by the store)
+  const long long c = min(c0 + (tid & (COLS - 1)), ncols - 1);
+  const int ky = (int)(c / nxw), kx = (int)(c - (long long)ky * nxw) + kx0;
+  const T axy = ax[kx] + ay[ky];
+  const bool zero_col = kx == 0 && ky == 0;
+  __syncthreads();
+  mbar_wait(bar, 0);
+  zsolve_tile<T, COLS>(s, tw, azr, nz, lnz, rad, tid, nt, axy, negN, zero_col);
   fence_proxy_async();  // the tile written by all threads becomes visible to the bulk store
   __syncthreads();
   if (tid == 0) {
     for (int z = 0; z < nz; z += rows) tma_store_2d(&tm, s + (size_t)z * COLS, (int)(2 * c0), z);
+    tma_store_commit_wait();
+  }
+}
+
+// -------------------------------------------------------------------------------------------------
+// k_zsolve_peer: the same solve for a slab-decomposed grid, FUSED with both transposes of the distributed
+// FFT.  Rank r owns the kx range [kx0, kx0+kxl) for all ky and all z; the z range [q*nzl, (q+1)*nzl) of a
+// column lives in rank q's in-slab spectrum S_q[zl][ky][kx] (row pitch nxp).  The block's tile
+// [nz][CY x CX columns] is gathered by TMA straight from the P peers' buffers over NVLink (one 3-D box per
+// peer and 256 planes), solved in shared memory and scattered back the same way: no packed copy of the
+// spectrum exists, and the NVLink transfers of one tile overlap the arithmetic of the others.
+// maps.m[q]: tensor (2*kxl words, ny, nzl) over S_q starting at column kx0, box (2*CX, CY, min(nzl,256)).
+// local_load = 1 ("push only"): the forward transpose was done by k_fft_scatter_fwd (peer STORES, which NVLink
+// moves faster than the 64-byte-row peer LOADS of a tile gather); the tile is then read from the local
+// transposed copy through `lmap` (tensor (2*kxl, ny, nz), same box) and only the way back is fused.
+// -------------------------------------------------------------------------------------------------
+struct PeerMaps {
+  CUtensorMap m[8];
+};
+
+template <typename T, int COLS>
+__global__ void __launch_bounds__(512) k_zsolve_peer(const __grid_constant__ PeerMaps maps, const __grid_constant__ CUtensorMap lmap,
+                                                     int local_load, const Cx<T> *__restrict__ twg,
+                                                     const T *__restrict__ ax, const T *__restrict__ ay,
+                                                     const T *__restrict__ az, int nz, int nzl, int P, int lcx, int tiles_x,
+                                                     int kxl, int kx0, int ny, T negN, ZRadix rad) {
+  extern __shared__ unsigned char zs_raw[];
+  unsigned char *zb = zs_raw + ((128u - (smem_u32(zs_raw) & 127u)) & 127u);
+  Cx<T> *s = reinterpret_cast<Cx<T> *>(zb);       // [nz][COLS], column = dy*CX + dx
+  Cx<T> *tw = s + (size_t)nz * COLS;              // [nz]
+  T *azr = reinterpret_cast<T *>(tw + nz);        // [nz]
+  uint64_t *bar = reinterpret_cast<uint64_t *>(azr + nz);
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int CX = 1 << lcx, CY = COLS >> lcx;
+  const int ty_ = blockIdx.x / tiles_x, tx_ = blockIdx.x - ty_ * tiles_x;
+  const int cx0 = tx_ * CX, ky0 = ty_ * CY;
+  const int rows = nzl < 256 ? nzl : 256;
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+    mbar_expect_tx(bar, (uint32_t)((size_t)nz * COLS * sizeof(Cx<T>)));
+    if (local_load) {  // the transposed copy [z global][ky][kx local] made by k_fft_scatter_fwd (box rows = `rows` as well)
+      for (int z = 0; z < nz; z += rows) tma_load_3d(s + (size_t)z * COLS, &lmap, bar, 2 * cx0, ky0, z);
+    } else {
+      for (int q = 0; q < P; q++)
+        for (int z = 0; z < nzl; z += rows) tma_load_3d(s + (size_t)(q * nzl + z) * COLS, &maps.m[q], bar, 2 * cx0, ky0, z);
+    }
+  }
+  int lnz = 0;
+  while ((1 << lnz) < nz) lnz++;
+  zsolve_tables<T>(tw, azr, twg, az, nz, lnz, rad, tid, nt);
+  const int col = tid & (COLS - 1), dy = col >> lcx, dx = col & (CX - 1);
+  const int kx = kx0 + min(cx0 + dx, kxl - 1), ky = min(ky0 + dy, ny - 1);  // clipped columns: any valid table entry
+  const T axy = ax[kx] + ay[ky];
+  const bool zero_col = kx == 0 && ky == 0;
+  __syncthreads();
+  mbar_wait(bar, 0);
+  zsolve_tile<T, COLS>(s, tw, azr, nz, lnz, rad, tid, nt, axy, negN, zero_col);
+  fence_proxy_async();
+  __syncthreads();
+  if (tid == 0) {
+    for (int q = 0; q < P; q++)
+      for (int z = 0; z < nzl; z += rows) tma_store_3d(&maps.m[q], s + (size_t)(q * nzl + z) * COLS, 2 * cx0, ky0, z);
     tma_store_commit_wait();
   }
 }

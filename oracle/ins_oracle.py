@@ -624,6 +624,70 @@ def RK44(T=np.float64):
     return runge_kutta_method(A, b, c, 0, T=T)
 
 
+def LMWray3(T=np.float64):
+    """LMWray3 low-storage method (src/time_steppers/methods.jl; coefficients step_lmwray3.jl:77-79)."""
+    return SimpleNamespace(lowstorage=True, a=(T(8 / 15), T(5 / 12), T(3 / 4)), b=(T(1 / 4), T(0)),
+                           c=(T(0), T(8 / 15), T(2 / 3)), T=T)
+
+
+def timestep_lmwray3(method, stepper, dt, theta=None):
+    """timestep!(::LMWray3, ...) src/time_steppers/step_lmwray3.jl:4-104 (velocity only): two state
+    registers (x, xstart) and one derivative register, exactly the reference's sequence of calls."""
+    setup, psolver, u, t, n = stepper.setup, stepper.psolver, stepper.u, stepper.t, stepper.n
+    T = setup.grid.T
+    dt = T(dt)
+    m = setup.closure_model
+    tstart = t
+    xstart = u.copy(order="F")                               # state_copyto!(xstart, x)  :61
+    a, b, c = method.a, method.b, method.c
+    nstage = len(a)
+    for i in range(nstage):
+        t = T(tstart + c[i] * dt)                            # :83
+        u = apply_bc_u(u, t, setup, copy=False)              # f!: :17
+        dx = momentum(u, None, t, setup)                     # :19
+        if m is not None:
+            dx = dx + m(u, theta)                            # :22
+        u = xstart.copy(order="F")                           # :87
+        u = u + T(a[i] * dt) * dx                            # :88  axpy!(a[i]*dt, dx, x)
+        u = apply_bc_u(u, t, setup, copy=False)              # correct!: :38
+        u = project(u, setup, psolver)                       # :39
+        if i != nstage - 1:
+            xstart = xstart + T(b[i] * dt) * dx              # :93
+    t = T(tstart + dt)                                       # :97
+    u = apply_bc_u(u, t, setup, copy=False)                  # :102
+    return create_stepper(method, setup, psolver, u, None, t, n + 1)
+
+
+# Explicit tableaux of src/time_steppers/RKMethods.jl used by the parity tests (file:line in the comments);
+# (A, b, c or None = row sums, r) BEFORE the shift of runge_kutta_method.
+_S6 = float(np.sqrt(6.0))
+EXPLICIT_TABLEAUX = {
+    "FE11": ([[0]], [1], [0], 1),                                                                   # :45-51
+    "SSP22": ([[0, 0], [1, 0]], [0.5, 0.5], None, 1),                                               # :54-60
+    "SSP33": ([[0, 0, 0], [1, 0, 0], [0.25, 0.25, 0]], [1 / 6, 1 / 6, 2 / 3], None, 1),             # :73-79
+    "SSP43": ([[0, 0, 0, 0], [0.5, 0, 0, 0], [0.5, 0.5, 0, 0], [1 / 6, 1 / 6, 1 / 6, 0]], [1 / 6, 1 / 6, 1 / 6, 0.5], None, 2),  # :82-88
+    "Wray3": ([[0, 0, 0], [8 / 15, 0, 0], [8 / 15 - 17 / 60, 5 / 12, 0]], [8 / 15 - 17 / 60, 0, 0.75],
+              [0, 8 / 15, 8 / 15 - 17 / 60 + 5 / 12], 0),                                           # :137-146
+    "RK56": ([[0] * 6, [0.25, 0, 0, 0, 0, 0], [0.125, 0.125, 0, 0, 0, 0], [0, 0, 0.5, 0, 0, 0],
+              [3 / 16, -3 / 8, 3 / 8, 9 / 16, 0, 0], [-3 / 7, 8 / 7, 6 / 7, -12 / 7, 8 / 7, 0]],
+             [7 / 90, 0, 16 / 45, 2 / 15, 16 / 45, 7 / 90], [0, 0.25, 0.25, 0.5, 0.75, 1], 0),       # :149-162
+    "HEM5": ([[0] * 5, [0.3, 0, 0, 0, 0], [(1 + _S6) / 30, (11 - 4 * _S6) / 30, 0, 0, 0],
+              [(-79 - 31 * _S6) / 150, (-1 - 4 * _S6) / 30, (24 + 11 * _S6) / 25, 0, 0],
+              [(14 + 5 * _S6) / 6, (-8 + 7 * _S6) / 6, (-9 - 7 * _S6) / 4, (9 - _S6) / 4, 0]],
+             [0, 0, (16 - _S6) / 36, (16 + _S6) / 36, 1 / 9], None, 0),                             # :253-265
+    "RK33C2": ([[0, 0, 0], [2 / 3, 0, 0], [1 / 3, 1 / 3, 0]], [0.25, 0, 0.75], [0, 2 / 3, 2 / 3], 0),  # :497-503
+    "RK44": ([[0, 0, 0, 0], [0.5, 0, 0, 0], [0, 0.5, 0, 0], [0, 0, 1, 0]], [1 / 6, 1 / 3, 1 / 3, 1 / 6], None, 0),  # :515-521
+    "RK44P2": ([[0, 0, 0, 0], [1, 0, 0, 0], [3 / 8, 1 / 8, 0, 0], [-1 / 8, -3 / 8, 1.5, 0]], [1 / 6, -1 / 18, 2 / 3, 2 / 9], [0, 1, 0.5, 1], 0),  # :542-548
+    "NSSP53": ([[0] * 5, [1 / 7, 0, 0, 0, 0], [0, 3 / 16, 0, 0, 0], [0, 0, 1 / 3, 0, 0], [0, 0, 0, 2 / 3, 0]],
+               [0.25, 0, 0, 0, 0.75], [0, 1 / 7, 3 / 16, 1 / 3, 2 / 3], 0),                          # :627-641
+}
+
+
+def explicit_method(name, T=np.float64):
+    A, b, c, r = EXPLICIT_TABLEAUX[name]
+    return runge_kutta_method(A, b, np.sum(np.array(A, dtype=np.float64), axis=1) if c is None else c, r, T=T)
+
+
 def create_stepper(method, setup, psolver, u, temp=None, t=0.0, n=0):
     """create_stepper src/time_steppers/step_explicit_runge_kutta.jl:1-2."""
     return SimpleNamespace(setup=setup, psolver=psolver, u=u, temp=temp, t=setup.grid.T(t), n=n)

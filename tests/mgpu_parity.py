@@ -52,6 +52,8 @@ def main():
         sc = ins.Setup(x, Re=T(800), bodyforce=bf, backend=backend)
         if "MGPU_P2P" in os.environ:  # A/B: 0 = NCCL send/recv transposes, 1 = peer-memory scatter
             sc.ctx.call("insb200_set_param", b"p2p", float(os.environ["MGPU_P2P"]))
+        if "MGPU_FUSED" in os.environ:  # A/B: 0 = scatter kernels + k_zsolve, 1 = k_zsolve_peer (gathers over NVLink itself)
+            sc.ctx.call("insb200_set_param", b"p2p_fused", float(os.environ["MGPU_FUSED"]))
         if theta is not None:
             so.closure_model = o.smagorinsky_closure(so)
             sc.closure_model = ins.smagorinsky_closure(sc)

@@ -229,7 +229,8 @@ def test_kernel_variants_bit_identical(T, smag):
                          ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1)),
                          ("tma_smag_v2_zc128", dict(variant=2, smag_v=2, smag_zchunk=128)),
                          ("tma_smag_v2_zc7", dict(variant=2, smag_v=2, smag_zchunk=7)),
-                         ("tma_smag_v2_zc2", dict(variant=2, smag_v=2, smag_zchunk=2))]:
+                         ("tma_smag_v2_zc2", dict(variant=2, smag_v=2, smag_zchunk=2)),
+                         ("tma_smag_v2_ty8", dict(variant=2, smag_v=2, smag_zchunk=16, smag_ty=8))]:
         for k, v in params.items():
             set_param(sc, k, v)
         u = ins.to_device(u0, sc)
