@@ -410,6 +410,10 @@ def run_ours(args, wl):
     barrier()
     timers = read_timers(setup)
     setup.ctx.call("insb200_set_profiling", 0)
+    if os.environ.get("BENCH_RANK_TIMERS"):  # per-rank view of the communication timers (stderr), for load-balance checks
+        sel = ("fft_pack_unpack", "fft_alltoall", "halo_exchange", "cufft_forward", "poisson_scale")
+        print(f"[rank {rank}] " + "  ".join(f"{k}={timers[k][0] / max(timers[k][1], 1):.3f}ms" for k in sel if k in timers),
+              file=sys.stderr, flush=True)
     esz = np.dtype(T).itemsize
     cells_local = cells / world
     nz_glob = n[-1]

@@ -81,6 +81,14 @@ struct insb200_ctx {
   int rank = 0, nranks = 1;
   int variant = 2;         // 0: one thread per cell, 1: LDG-tiled stage kernel, 2: TMA plane pipeline (3-D)
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
+  int fft_pipe = 4;        // param: nranks > 1, peer transposes: the slab is transformed in this many z-chunks and the scatter of
+                           // one chunk overlaps the cuFFT of the next on a second stream (1 = no pipelining)
+  int fft_pipe_min_ranks = 4;
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t pipe_ev[16] = {nullptr}, pipe_sync = nullptr;
+  int fft_chunk = 0;       // param: planes per in-plane cuFFT exec (0 = the whole slab); small chunks keep the x->y intermediate in L2
+  int fft_batch = 0;       // planes per exec of plan_fwd_in / plan_inv_in as planned
+  long long fft_cdist = 0; // complex words between consecutive planes of the in-slab spectrum
   int smag_v = 2;          // closure kernel: 1 = shared-memory stencil (k_smag3d_tma), 2 = register-carried (k_smag3d_v2)
   int smag_ty = 16;        // tile height of k_smag3d_v2: 16 (one 640-thread block per SM) or 8 (two 384-thread blocks)
   int smag_zchunk = 128;   // planes marched per block of k_smag3d_v2

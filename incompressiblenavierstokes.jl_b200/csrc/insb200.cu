@@ -271,6 +271,12 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
       if (q != c->rank && c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
     }
   }
+  if (c->comm_stream) {
+    cudaStreamSynchronize(c->comm_stream);
+    for (auto &e : c->pipe_ev) if (e) cudaEventDestroy(e);
+    if (c->pipe_sync) cudaEventDestroy(c->pipe_sync);
+    cudaStreamDestroy(c->comm_stream);
+  }
   if (c->barbuf) cudaFree(c->barbuf);
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
@@ -403,8 +409,10 @@ static int ensure_fft(insb200_ctx *c) {
       int remb[2] = {c->ext[1], c->ext[0]};
       int cemb[2] = {c->nloc[1], c->nxh};
       const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxh;
-      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
-      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
+      c->fft_batch = (c->fft_chunk > 0 && c->nloc[2] % c->fft_chunk == 0) ? c->fft_chunk : c->nloc[2];
+      c->fft_cdist = cdist;
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->fft_batch));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->fft_batch));
       INS_CUFFT(c, cufftSetStream(c->plan_fwd_in, c->stream));
       INS_CUFFT(c, cufftSetStream(c->plan_inv_in, c->stream));
     }
@@ -421,8 +429,13 @@ static int ensure_fft(insb200_ctx *c) {
       int remb[2] = {c->ext[1], c->ext[0]};
       int cemb[2] = {c->nloc[1], c->nxp};
       const int rdist = (int)c->csz, cdist = c->nloc[1] * c->nxp;
-      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[2]));
-      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->nloc[2]));
+      c->fft_batch = (c->fft_chunk > 0 && c->nloc[2] % c->fft_chunk == 0) ? c->fft_chunk : c->nloc[2];
+      // (measured: +2 % at 8 GPUs, -1 % at 2 GPUs, where the scatter competes with cuFFT for HBM: used from 4 ranks on)
+      if (c->fft_chunk <= 0 && c->p2p_enable && c->nranks >= c->fft_pipe_min_ranks && c->fft_pipe > 1 && c->fft_pipe <= 16 && c->nloc[2] % c->fft_pipe == 0 && c->nloc[2] / c->fft_pipe >= 8)
+        c->fft_batch = c->nloc[2] / c->fft_pipe;  // z-chunks of the transform / transpose pipeline
+      c->fft_cdist = cdist;
+      INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 2, nn, remb, 1, rdist, cemb, 1, cdist, f32 ? CUFFT_R2C : CUFFT_D2Z, c->fft_batch));
+      INS_CUFFT(c, cufftPlanMany(&c->plan_inv_in, 2, nn, cemb, 1, cdist, remb, 1, rdist, f32 ? CUFFT_C2R : CUFFT_Z2D, c->fft_batch));
     } else {
       int nn[1] = {c->nloc[0]};
       INS_CUFFT(c, cufftPlanMany(&c->plan_fwd_in, 1, nn, nullptr, 1, 0, nullptr, 1, 0, f32 ? CUFFT_R2C : CUFFT_D2Z, c->nloc[1]));
@@ -556,6 +569,34 @@ static int bc_fill(insb200_ctx *c, void *base, int nc) {
 }
 
 // ---- fused last-axis transform + symbol + inverse (zsolve.cuh) --------------------------------------
+// in-plane (x, y) transforms of the slab, `fft_batch` planes per cuFFT exec
+template <typename T, typename C>
+static int exec_fwd_in(insb200_ctx *c, T *pr, C *S) {
+  ScopedTimer tm(c, TM_FFT_FWD);
+  const int nb = (c->D == 3 && c->fft_batch > 0) ? c->nloc[2] / c->fft_batch : 1;
+  for (int b = 0; b < nb; b++) {
+    T *r = pr + (i64)b * c->fft_batch * c->csz;
+    C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
+    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)r, (cufftComplex *)s));
+    else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)r, (cufftDoubleComplex *)s));
+  }
+  c->fft_execs++;
+  return 0;
+}
+template <typename T, typename C>
+static int exec_inv_in(insb200_ctx *c, C *S, T *pr) {
+  ScopedTimer tm(c, TM_FFT_INV);
+  const int nb = (c->D == 3 && c->fft_batch > 0) ? c->nloc[2] / c->fft_batch : 1;
+  for (int b = 0; b < nb; b++) {
+    T *r = pr + (i64)b * c->fft_batch * c->csz;
+    C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
+    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)s, (cufftReal *)r));
+    else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)s, (cufftDoubleReal *)r));
+  }
+  c->fft_execs++;
+  return 0;
+}
+
 static bool zsolve_supported(const insb200_ctx *c) {
   const int nz = c->nglob[2];
   return c->D == 3 && c->zsolve && nz >= 8 && nz <= 2048 && (nz & (nz - 1)) == 0;
@@ -714,19 +755,9 @@ static int poisson_solve(insb200_ctx *c) {
   const double ntot = (double)c->nglob[0] * c->nglob[1] * (D == 3 ? c->nglob[2] : 1);
   const T invN = T(1) / T(ntot);
   if (c->nranks == 1 && D == 3 && zsolve_supported(c)) {
-    {
-      ScopedTimer tm(c, TM_FFT_FWD);
-      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)pr, (cufftComplex *)S));
-      else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
-      c->fft_execs++;
-    }
+    INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
     INS_TRY((launch_zsolve<T>(c, S, (i64)c->nloc[1] * c->nxh, c->nxh, 0, invN)));
-    {
-      ScopedTimer tm(c, TM_FFT_INV);
-      if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
-      else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
-      c->fft_execs++;
-    }
+    INS_TRY((exec_inv_in<T, C>(c, S, pr)));
     return 0;
   }
   if (c->nranks == 1) {
@@ -757,12 +788,9 @@ static int poisson_solve(insb200_ctx *c) {
   const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
   auto chunk_w = [&](int q) { return std::max(0, std::min((q + 1) * c->kxc, c->nxh) - q * c->kxc); };
   dim3 pblk(64, 4, 1), pgrd((unsigned)((rows + 3) / 4), (c->nxh + 63) / 64, 1);
-  {
-    ScopedTimer tm(c, TM_FFT_FWD);
-    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)pr, (cufftComplex *)S));
-    else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)pr, (cufftDoubleComplex *)S));
-    c->fft_execs++;
-  }
+  dim3 sgrd((unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), c->nranks, 1);  // scatter kernels: y = destination
+  const bool pipelined = c->p2p && !c->p2p_fused && D == 3 && zsolve_supported(c) && c->fft_pipe > 1 && c->fft_batch * c->fft_pipe == c->nloc[2];
+  if (!pipelined) INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
   C *W = c->p2p ? B : S;  // the transposed spectrum (kxl fastest, ky, global z) of this rank
   auto peer_barrier = [&]() -> int {  // all ranks' peer stores issued so far are complete and visible afterwards
     INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
@@ -770,28 +798,79 @@ static int poisson_solve(insb200_ctx *c) {
   };
   PeerPtrs pS, pB;
   for (int q = 0; q < 16; q++) { pS.p[q] = c->peerS[q]; pB.p[q] = c->peerB[q]; }
+  if (pipelined) {
+    // ---- pipelined: the slab is transformed in fft_pipe z-chunks; the peer scatter of chunk b runs on a second
+    // stream while cuFFT works on chunk b+1 (forward), and the C2R of chunk b while chunk b+1 is scattered back
+    const int NB = c->fft_pipe;
+    const i64 rb = (i64)c->fft_batch * c->nloc[1];  // rows per chunk
+    if (!c->comm_stream) {
+      INS_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+      for (int b = 0; b < 16; b++) INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_ev[b], cudaEventDisableTiming));
+      INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_sync, cudaEventDisableTiming));
+    }
+    dim3 sg((unsigned)((rb + 4 * kScatterRows - 1) / (4 * kScatterRows)), c->nranks, 1);
+    {
+      ScopedTimer tm(c, TM_FFT_FWD);
+      for (int b = 0; b < NB; b++) {
+        T *r = pr + (i64)b * c->fft_batch * c->csz;
+        C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
+        if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)r, (cufftComplex *)s));
+        else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)r, (cufftDoubleComplex *)s));
+        INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->stream));
+        INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_ev[b], 0));
+        k_fft_scatter_fwd<C><<<sg, pblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, 0, b * rb, (b + 1) * rb);
+        CHECK_LAUNCH(c);
+      }
+      c->fft_execs++;
+    }
+    {
+      ScopedTimer tm(c, TM_A2A);
+      INS_CUDA(c, cudaEventRecord(c->pipe_sync, c->comm_stream));
+      INS_CUDA(c, cudaStreamWaitEvent(c->stream, c->pipe_sync, 0));
+      INS_TRY(peer_barrier());
+    }
+    if (c->kxl > 0) INS_TRY((launch_zsolve<T>(c, B, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
+    INS_CUDA(c, cudaEventRecord(c->pipe_sync, c->stream));
+    INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_sync, 0));
+    for (int b = 0; b < NB; b++) {
+      if (c->kxl > 0) {
+        k_fft_scatter_bwd<C><<<sg, pblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, c->nranks, b * rb, (b + 1) * rb);
+        CHECK_LAUNCH(c);
+      }
+      INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->comm_stream));
+    }
+    {
+      ScopedTimer tm(c, TM_FFT_INV);
+      for (int b = 0; b < NB; b++) {
+        INS_CUDA(c, cudaStreamWaitEvent(c->stream, c->pipe_ev[b], 0));
+        INS_TRY(peer_barrier());  // chunk b of every rank's spectrum is complete
+        T *r = pr + (i64)b * c->fft_batch * c->csz;
+        C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
+        if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)s, (cufftReal *)r));
+        else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)s, (cufftDoubleReal *)r));
+      }
+      c->fft_execs++;
+    }
+    return 0;
+  }
   if (c->p2p && c->p2p_fused && D == 3 && zsolve_supported(c) && c->nranks <= 8) {
     // p2p_fused = 2: every rank gathers its kx range of the peers' spectra inside the solve kernel (peer loads);
     // p2p_fused = 1: the way there is k_fft_scatter_fwd (peer stores), only the way back is fused into the solve
     const bool local_load = c->p2p_fused == 1;
     if (local_load) {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, sizeof(T) == 4);
+      k_fft_scatter_fwd<C><<<sgrd, pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, sizeof(T) == 4, 0, rows);
       CHECK_LAUNCH(c);
     }
     { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all in-slab transforms / forward scatters are complete
     if (c->kxl > 0) INS_TRY((launch_zsolve_peer<T>(c, invN, local_load)));
     { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all peers' stores into this rank's spectrum are complete
-    ScopedTimer tm(c, TM_FFT_INV);
-    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
-    else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
-    c->fft_execs++;
-    return 0;
+    return exec_inv_in<T, C>(c, S, pr);
   }
   if (c->p2p) {
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_fwd<C><<<(unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, 0);
+      k_fft_scatter_fwd<C><<<sgrd, pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, 0, 0, rows);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
@@ -841,8 +920,7 @@ static int poisson_solve(insb200_ctx *c) {
   if (c->p2p) {
     if (c->kxl > 0) {
       ScopedTimer tm(c, TM_PACK);
-      const unsigned grd = (unsigned)((rows * c->nranks + 4 * kScatterRows - 1) / (4 * kScatterRows));
-      k_fft_scatter_bwd<C><<<grd, pblk, 0, c->stream>>>(pS, W, c->nxp, rows, c->kxl, c->kx0, c->nranks);
+      k_fft_scatter_bwd<C><<<sgrd, pblk, 0, c->stream>>>(pS, W, c->nxp, rows, c->kxl, c->kx0, c->rank, c->nranks, 0, rows);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
@@ -864,12 +942,7 @@ static int poisson_solve(insb200_ctx *c) {
       CHECK_LAUNCH(c);
     }
   }
-  {
-    ScopedTimer tm(c, TM_FFT_INV);
-    if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)S, (cufftReal *)pr));
-    else INS_CUFFT(c, cufftExecZ2D(c->plan_inv_in, (cufftDoubleComplex *)S, (cufftDoubleReal *)pr));
-    c->fft_execs++;
-  }
+  INS_TRY((exec_inv_in<T, C>(c, S, pr)));
   return 0;
 }
 
@@ -1744,6 +1817,16 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
   else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
+  else if (k == "fft_pipe") {
+    if (c->plans) INS_FAIL(c, "fft_pipe must be set before the first pressure solve");
+    if (v < 1 || v > 16) INS_FAIL(c, "fft_pipe must be in [1, 16]");
+    c->fft_pipe = v;
+  }
+  else if (k == "fft_pipe_min_ranks") c->fft_pipe_min_ranks = v;
+  else if (k == "fft_chunk") {
+    if (c->plans) INS_FAIL(c, "fft_chunk must be set before the first pressure solve");
+    c->fft_chunk = v;
+  }
   else if (k == "smag_ty") { if (v != 8 && v != 16) INS_FAIL(c, "smag_ty must be 8 or 16"); c->smag_ty = v; }
   else if (k == "smag_zchunk") { if (v < 2) INS_FAIL(c, "smag_zchunk must be >= 2"); c->smag_zchunk = v; }
   else if (k == "p2p_fused") { if (v < 0 || v > 2) INS_FAIL(c, "p2p_fused must be 0, 1 or 2"); c->p2p_fused = v; }

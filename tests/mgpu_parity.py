@@ -24,6 +24,7 @@ CASES = [
     ((32, 16, 16), np.float64, False, None, 4, 2e-3),        # TMA path, slabs of 8 (or fewer) planes
     ((32, 16, 32), np.float32, True, 0.17, 4, 1e-3),         # TMA path + closure + force
     ((24, 20, 16), np.float64, False, 0.17, 3, 2e-3),        # generic path (not tile aligned)
+    ((64, 32, 64), np.float32, False, 0.17, 2, 1e-3),        # 8 planes per rank at 8 GPUs, closure kernel v2
 ]
 
 
@@ -52,6 +53,7 @@ def main():
         sc = ins.Setup(x, Re=T(800), bodyforce=bf, backend=backend)
         if "MGPU_P2P" in os.environ:  # A/B: 0 = NCCL send/recv transposes, 1 = peer-memory scatter
             sc.ctx.call("insb200_set_param", b"p2p", float(os.environ["MGPU_P2P"]))
+        sc.ctx.call("insb200_set_param", b"fft_pipe_min_ranks", 2.0)  # exercise the pipelined transposes at any world size
         if "MGPU_FUSED" in os.environ:  # A/B: 0 = scatter kernels + k_zsolve, 1 = k_zsolve_peer (gathers over NVLink itself)
             sc.ctx.call("insb200_set_param", b"p2p_fused", float(os.environ["MGPU_FUSED"]))
         if theta is not None:

@@ -29,9 +29,12 @@ def slab_bounds(n_last, rank, nranks):
     return rank * m, (rank + 1) * m
 
 
-def kx_chunk(nxh, rank, nranks):
-    """insb200_create: kxc = ceil(nxh / nranks); rank owns kx in [rank*kxc, min((rank+1)*kxc, nxh))."""
+def kx_chunk(nxh, rank, nranks, even=False):
+    """insb200_create: kxc = ceil(nxh / nranks) (rounded up to an even number in Float32 so that chunk starts are
+    16-byte aligned); rank owns kx in [rank*kxc, min((rank+1)*kxc, nxh))."""
     kxc = (nxh + nranks - 1) // nranks
+    if even:
+        kxc = (kxc + 1) & ~1
     lo = min(rank * kxc, nxh)
     return kxc, lo, min((rank + 1) * kxc, nxh) - lo
 
