@@ -89,6 +89,16 @@ int insb200_smagorinsky(insb200_ctx *ctx, void *s, const void *u, double theta);
 
 /* divergence!(div, u, setup): src/operators.jl:106-125 (interior written, ghosts untouched) */
 int insb200_divergence(insb200_ctx *ctx, void *div, const void *u);
+/* Observer fields (observefield, src/processors.jl:77-198), single rank, reference layout:
+ * vorticity!(w, u, setup): src/operators.jl:989-1021 -- w is a scalar field in 2-D, a vector field in 3-D; written on
+ *   indices 1..N-1 of every axis (Julia, 1-based), the ghosts of u must be valid (apply_bc_u! first, processors.jl:153);
+ * interpolate_u_p!(up, u, setup): src/operators.jl:1311-1326 (Ip written);
+ * interpolate_w_p!(wp, w, setup): src/operators.jl:1338-1372 (Ip written; wp scalar in 2-D, vector in 3-D);
+ * velocitynorm: `@. upnorm = sqrt(up1^2 + up2^2 [+ up3^2])` over the whole array, src/processors.jl:141-151. */
+int insb200_vorticity(insb200_ctx *ctx, void *w, const void *u);
+int insb200_interpolate_u_p(insb200_ctx *ctx, void *up, const void *u);
+int insb200_interpolate_w_p(insb200_ctx *ctx, void *wp, const void *w);
+int insb200_velocitynorm(insb200_ctx *ctx, void *out, const void *up);
 /* scalewithvolume!(p, setup): src/operators.jl:81-95 (whole array incl. ghosts) */
 int insb200_scalewithvolume(insb200_ctx *ctx, void *p);
 /* pressuregradient!(G, p, setup): src/operators.jl:159-178 (interior written) */

@@ -51,6 +51,10 @@ PROTOTYPES = {
     "insb200_reset_timers": (c_int, [c_void_p]),
     "insb200_set_variant": (c_int, [c_void_p, c_int]),
     "insb200_set_param": (c_int, [c_void_p, C.c_char_p, c_double]),
+    "insb200_vorticity": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_interpolate_u_p": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_interpolate_w_p": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_velocitynorm": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_workspace_bytes": (c_ll, [c_void_p]),
 }
 

@@ -27,7 +27,8 @@ __all__ = [
     "diffusion", "convectiondiffusion", "divergence_", "divergence", "scalewithvolume_",
     "pressuregradient_", "pressuregradient", "applypressure_", "applypressure", "psolver_spectral",
     "default_psolver", "poisson_", "poisson", "project_", "project", "pressure_", "pressure",
-    "smagorinsky_closure", "total_kinetic_energy", "get_cfl_timestep_", "maxabs", "RKMethods", "LMWray3",
+    "smagorinsky_closure", "vorticity_", "vorticity", "interpolate_u_p_", "interpolate_u_p", "interpolate_w_p_",
+    "interpolate_w_p", "velocitynorm_", "total_kinetic_energy", "get_cfl_timestep_", "maxabs", "RKMethods", "LMWray3",
     "runge_kutta_method", "ode_method_cache", "create_stepper", "timestep_", "solve_unsteady",
     "solve_unsteady_host", "init_distributed", "local_slab", "gather_slabs",
 ]
@@ -312,6 +313,52 @@ def divergence_(div, u, setup):
 
 def divergence(u, setup):
     return divergence_(scalarfield(setup), u, setup)
+
+
+def _wfield(setup):
+    """vorticity is a scalar field in 2-D and a vector field in 3-D (operators.jl:978-983)"""
+    return scalarfield(setup) if setup.grid.dimension == 2 else vectorfield(setup)
+
+
+def vorticity_(w, u, setup):
+    """vorticity!(w, u, setup)  src/operators.jl:985-1021 (ghosts of u must be valid)"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_vorticity", _ptr(_check(w, setup, setup.grid.dimension == 3)), _ptr(_check(u, setup, True)))
+    return w
+
+
+def vorticity(u, setup):
+    return vorticity_(_wfield(setup), u, setup)
+
+
+def interpolate_u_p_(up, u, setup):
+    """interpolate_u_p!(up, u, setup)  src/operators.jl:1311-1326"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_interpolate_u_p", _ptr(_check(up, setup, True)), _ptr(_check(u, setup, True)))
+    return up
+
+
+def interpolate_u_p(u, setup):
+    return interpolate_u_p_(vectorfield(setup), u, setup)
+
+
+def interpolate_w_p_(wp, w, setup):
+    """interpolate_w_p!(wp, w, setup)  src/operators.jl:1338-1372"""
+    vec = setup.grid.dimension == 3
+    _sync_stream(setup)
+    setup.ctx.call("insb200_interpolate_w_p", _ptr(_check(wp, setup, vec)), _ptr(_check(w, setup, vec)))
+    return wp
+
+
+def interpolate_w_p(w, setup):
+    return interpolate_w_p_(_wfield(setup), w, setup)
+
+
+def velocitynorm_(out, up, setup):
+    """`@. upnorm = sqrt(up1^2 + up2^2 [+ up3^2])`  src/processors.jl:141-151"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_velocitynorm", _ptr(_check(out, setup, False)), _ptr(_check(up, setup, True)))
+    return out
 
 
 def scalewithvolume_(p, setup):

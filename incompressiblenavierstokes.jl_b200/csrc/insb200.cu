@@ -1048,6 +1048,32 @@ static int op_divergence(insb200_ctx *c, void *div, const void *u) {
 }
 
 template <typename T, int D>
+static int op_vorticity(insb200_ctx *c, void *w, const void *u) {
+  ScopedTimer tm(c, TM_MISC);
+  const int N0 = c->nloc[0] + 2, N1 = c->nloc[1] + 2, N2 = D == 3 ? c->nloc[2] + 2 : 1;
+  dim3 blk(64, 4, 1), grd((N0 - 1 + 63) / 64, (N1 - 1 + 3) / 4, D == 3 ? N2 - 1 : 1);
+  k_vorticity<T, D><<<grd, blk, 0, c->stream>>>((T *)w, (const T *)u, N0, N1, N2, make_rh<T>(c));
+  CHECK_LAUNCH(c);
+  return 0;
+}
+template <typename T, int D>
+static int op_interp_p(insb200_ctx *c, void *out, const void *in, int mode) {
+  ScopedTimer tm(c, TM_MISC);
+  if (mode == 0) k_interp_p<T, D, 0><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_ghosted<T>(c, out), view_ghosted_c<T>(c, in), geo_ghosted(c));
+  else k_interp_p<T, D, 1><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(view_ghosted<T>(c, out), view_ghosted_c<T>(c, in), geo_ghosted(c));
+  CHECK_LAUNCH(c);
+  return 0;
+}
+template <typename T, int D>
+static int op_velocitynorm(insb200_ctx *c, void *out, const void *up) {
+  ScopedTimer tm(c, TM_MISC);
+  const i64 n = ghosted_elems(c);
+  k_velocitynorm<T, D><<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>((T *)out, (const T *)up, n);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T, int D>
 static int op_scalewithvolume(insb200_ctx *c, void *p) {
   ScopedTimer tm(c, TM_MISC);
   const i64 n = ghosted_elems(c);
@@ -1214,6 +1240,34 @@ extern "C" int insb200_divergence(insb200_ctx *c, void *div, const void *u) {
   API_PROLOG(c);
   if (!div || !u) INS_FAIL(c, "NULL field");
   return DISPATCH(c, op_divergence, c, div, u);
+}
+static int observers_single_rank(insb200_ctx *c) {
+  if (c->nranks > 1) INS_FAIL(c, "observer fields are computed per slab by the caller: not available with nranks > 1 yet");
+  return 0;
+}
+extern "C" int insb200_vorticity(insb200_ctx *c, void *w, const void *u) {
+  API_PROLOG(c);
+  if (!w || !u) INS_FAIL(c, "NULL field");
+  INS_TRY(observers_single_rank(c));
+  return DISPATCH(c, op_vorticity, c, w, u);
+}
+extern "C" int insb200_interpolate_u_p(insb200_ctx *c, void *up, const void *u) {
+  API_PROLOG(c);
+  if (!up || !u) INS_FAIL(c, "NULL field");
+  INS_TRY(observers_single_rank(c));
+  return DISPATCH(c, op_interp_p, c, up, u, 0);
+}
+extern "C" int insb200_interpolate_w_p(insb200_ctx *c, void *wp, const void *w) {
+  API_PROLOG(c);
+  if (!wp || !w) INS_FAIL(c, "NULL field");
+  INS_TRY(observers_single_rank(c));
+  return DISPATCH(c, op_interp_p, c, wp, w, 1);
+}
+extern "C" int insb200_velocitynorm(insb200_ctx *c, void *out, const void *up) {
+  API_PROLOG(c);
+  if (!out || !up) INS_FAIL(c, "NULL field");
+  INS_TRY(observers_single_rank(c));
+  return DISPATCH(c, op_velocitynorm, c, out, up);
 }
 extern "C" int insb200_scalewithvolume(insb200_ctx *c, void *p) {
   API_PROLOG(c);

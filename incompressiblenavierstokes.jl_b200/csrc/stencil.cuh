@@ -397,6 +397,59 @@ __global__ void k_gradient_z(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// observers (processors.jl:77-198): fields derived from u, on the reference layout (raw base pointer,
+// N = n+2 points per axis incl. ghosts; the ghosts of u must be valid).
+// ---------------------------------------------------------------------------------------------
+// vorticity!  src/operators.jl:989-1021: over ndrange N-1 (0-based indices 0 .. N-2 on every axis)
+//   2-D: w[I]   = (u[I+e1,2] - u[I,2])/h1 - (u[I+e2,1] - u[I,1])/h2
+//   3-D: w[I,a] = (u[I+e(a+),a-] - u[I,a-])/h(a+) - (u[I+e(a-),a+] - u[I,a+])/h(a-),  (a,a+,a-) cyclic
+template <typename T, int D>
+__global__ void k_vorticity(T *__restrict__ w, const T *__restrict__ u, int N0, int N1, int N2, Rh<T> rh) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, k = blockIdx.z;
+  if (i >= N0 - 1 || j >= N1 - 1 || (D == 3 && k >= N2 - 1)) return;
+  const i64 sy = N0, sz = (i64)N0 * N1, sc = (i64)N0 * N1 * (D == 3 ? N2 : 1);
+  const i64 o = i + j * sy + (D == 3 ? k * sz : 0);
+  const i64 e[3] = {1, sy, sz};
+  if (D == 2) {
+    w[o] = (u[sc + o + e[0]] - u[sc + o]) * rh.v[0] - (u[o + e[1]] - u[o]) * rh.v[1];
+  } else {
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+      const int ap = (a + 1) % 3, am = (a + 2) % 3;
+      w[a * sc + o] = (u[am * sc + o + e[ap]] - u[am * sc + o]) * rh.v[ap] - (u[ap * sc + o + e[am]] - u[ap * sc + o]) * rh.v[am];
+    }
+  }
+}
+
+// MODE 0: interpolate_u_p!  src/operators.jl:1311-1326:  up[I,a] = (u[I-e(a),a] + u[I,a]) / 2 on Ip
+// MODE 1: interpolate_w_p!  src/operators.jl:1338-1372:  2-D: wp[I] = (w[I-e1-e2] + w[I]) / 2;
+//                                                        3-D: wp[I,a] = (w[I-e(a+)-e(a-),a] + w[I,a]) / 2 on Ip
+template <typename T, int D, int MODE>
+__global__ void k_interp_p(View<T> out, View<const T> in, Geo g) {
+  INS_CELL_IDX(g)
+  const i64 o = k * in.sz + j * in.sy + i;
+  const i64 e[3] = {1, in.sy, in.sz};
+  const int nc = (MODE == 1 && D == 2) ? 1 : D;
+  for (int a = 0; a < nc; a++) {
+    i64 back;
+    if (MODE == 0) back = e[a];
+    else if (D == 2) back = e[0] + e[1];
+    else back = e[(a + 1) % 3] + e[(a + 2) % 3];
+    out.p[a * out.sc + o] = (in.p[a * in.sc + o - back] + in.p[a * in.sc + o]) * T(0.5);
+  }
+}
+
+// velocity norm of observefield(:velocitynorm), processors.jl:141-151: sqrt(up1^2 + up2^2 [+ up3^2]) over the whole array
+template <typename T, int D>
+__global__ void k_velocitynorm(T *__restrict__ out, const T *__restrict__ up, i64 n) {
+  const i64 t = (i64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n) return;
+  T s = up[t] * up[t] + up[n + t] * up[n + t];
+  if (D == 3) s = s + up[2 * n + t] * up[2 * n + t];
+  out[t] = sqrt(s);
+}
+
 // whole-array scale (scalewithvolume! on the reference layout, ghosts included)
 template <typename T>
 __global__ void k_scale(T *p, i64 n, T f) {

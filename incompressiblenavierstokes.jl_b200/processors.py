@@ -102,26 +102,120 @@ def energy_history(setup, nupdate=1):
 
 
 def observefield(setup, fieldname, nupdate=1, psolver=None):
-    """observefield(state; setup, fieldname)  src/processors.jl:77-198 for the fields that live on
-    the hot path: `:pressure` (pressure!) and `:velocity_raw` (u[Ip, :] as stored).  Returns host
-    arrays restricted to Ip."""
+    """observefield(state; setup, fieldname)  src/processors.jl:77-198 for `1 | 2 | 3` (one interpolated
+    velocity component), `:velocity`, `:velocitynorm`, `:vorticity`, `:pressure` -- all computed on the device
+    by the library -- and `:velocity_raw` (u[Ip, :] as stored).  Returns host arrays restricted to Ip."""
+    g = setup.grid
+    D = g.dimension
+    if fieldname not in (1, 2, 3, "velocity", "velocitynorm", "vorticity", "pressure", "velocity_raw"):
+        raise ValueError("Unknown fieldname")  # processors.jl:128
+    if fieldname in (1, 2, 3) and fieldname > D:
+        raise ValueError("Unknown fieldname")
 
     def initialize(state):
         out = []
-        g = setup.grid
+        up = api.vectorfield(setup) if fieldname in (1, 2, 3, "velocity", "velocitynorm") else None
+        upnorm = api.scalarfield(setup) if fieldname == "velocitynorm" else None
+        w = api._wfield(setup) if fieldname == "vorticity" else None
+        wp = api._wfield(setup) if fieldname == "vorticity" else None
 
         def on(s):
             if s.n % nupdate:
                 return
             if fieldname == "pressure":
-                p = api.pressure(s.u, None, s.t, setup, psolver)
-                out.append(api.to_host(p)[g.Ip].copy())
+                f = api.to_host(api.pressure(s.u, None, s.t, setup, psolver))[g.Ip]
             elif fieldname == "velocity_raw":
-                out.append(api.to_host(s.u)[g.Ip].copy())
-            else:
-                raise ValueError("Unknown fieldname")
+                f = api.to_host(s.u)[g.Ip]
+            elif fieldname in (1, 2, 3):
+                f = api.to_host(api.interpolate_u_p_(up, s.u, setup))[g.Ip + (fieldname - 1,)]
+            elif fieldname == "velocity":
+                f = api.to_host(api.interpolate_u_p_(up, s.u, setup))[g.Ip]
+            elif fieldname == "velocitynorm":
+                api.interpolate_u_p_(up, s.u, setup)
+                f = api.to_host(api.velocitynorm_(upnorm, up, setup))[g.Ip]
+            else:  # vorticity: processors.jl:152-155
+                api.apply_bc_u_(s.u, s.t, setup)
+                api.vorticity_(w, s.u, setup)
+                f = api.to_host(api.interpolate_w_p_(wp, w, setup))[g.Ip]
+            out.append(f.copy())
 
         state.on(on)
         return out
 
     return Processor(initialize, nupdate=nupdate)
+
+
+def spectral_stuff(setup, npoint=100, a=None):
+    """spectral_stuff(setup; npoint, a)  src/utils.jl:49-108: wavenumber shells of the energy spectrum.
+    `inds` are 0-based linear indices (first axis fastest) into the K1 x .. x KD block of low modes."""
+    g = setup.grid
+    D, T, Np = g.dimension, g.T, g.Np
+    a = T((1 + np.sqrt(5)) / 2) if a is None else T(a)
+    K = tuple(n // 2 for n in Np)
+    grids = np.meshgrid(*[np.arange(k, dtype=np.int64) for k in K], indexing="ij")
+    k = np.sqrt(sum(q.astype(np.float64) ** 2 for q in grids)).astype(T).reshape(-1, order="F")
+    kmax = min(K) - 1
+    isort = np.argsort(k, kind="stable")
+    ksort = k[isort]
+    kappa = np.exp(np.linspace(0.0, np.log(float(kmax)), npoint))
+    kappa = np.array(sorted({int(v) for v in np.round(kappa)}), dtype=np.int64)
+    inds = []
+    for ki in kappa:
+        if D == 2:  # dyadic binning
+            lo, hi = T(ki) / a, T(ki) * a
+        else:       # linear binning
+            lo, hi = T(ki) - T(0.01), T(ki) + T(1) - T(0.01)
+        inds.append(isort[int(np.searchsorted(ksort, T(lo), side="left")):int(np.searchsorted(ksort, T(hi), side="left"))])
+    return inds, kappa, K
+
+
+def observespectrum(setup, npoint=100, a=None, nupdate=1):
+    """observespectrum(state; setup, npoint, a)  src/processors.jl:303-332, on the device: per component a
+    complex FFT of u[Ip] (cuFFT through torch.fft, as the reference goes through CUDA.jl's CUFFT), |.|^2 of the
+    K1 x .. x KD low modes / (2 prod(Np)^2), summed over components and over each shell.  Single rank.
+    `finalize` returns (ehat history [nobs, nshell], kappa)."""
+    import torch
+
+    g = setup.grid
+    D, T, Np = g.dimension, g.T, g.Np
+    if getattr(setup.backend, "nranks", 1) > 1:
+        raise NotImplementedError("observespectrum needs the whole field on one device")
+    inds, kappa, K = spectral_stuff(setup, npoint, a)
+    dev = setup.device
+    shell = torch.full((int(np.prod(K)),), len(inds), dtype=torch.int64, device=dev)  # modes outside every shell -> dump bin
+    multi = np.zeros(int(np.prod(K)), dtype=np.int64)
+    for i, ix in enumerate(inds):
+        multi[ix] += 1
+    if multi.max() > 1:  # overlapping (dyadic, 2-D) shells: fall back to one masked sum per shell
+        masks = [torch.as_tensor(ix, device=dev) for ix in inds]
+    else:
+        masks = None
+        for i, ix in enumerate(inds):
+            shell[torch.as_tensor(ix, device=dev)] = i
+    scale = T(2 * int(np.prod(Np)) ** 2)
+    ctype = torch.complex64 if T == np.float32 else torch.complex128
+    interior = tuple(slice(1, n + 1) for n in reversed(Np))  # device fields are (comp, N_D, .., N_1)
+    low = tuple(slice(0, k) for k in reversed(K))
+
+    def initialize(state):
+        out = []
+
+        def on(s):
+            if s.n % nupdate:
+                return
+            e = None
+            for al in range(D):
+                uhat = torch.fft.fftn(s.u[(al,) + interior].to(ctype))[low]
+                ea = (uhat.real ** 2 + uhat.imag ** 2) / scale
+                e = ea if e is None else e + ea
+            ef = e.reshape(-1)  # C-order flatten of (K_D, .., K_1) == first axis fastest
+            if masks is None:
+                eh = torch.zeros(len(inds) + 1, dtype=ef.dtype, device=dev).index_add_(0, shell, ef)[:-1]
+            else:
+                eh = torch.stack([ef[m].sum() for m in masks])
+            out.append(eh.cpu().numpy())
+
+        state.on(on)
+        return out
+
+    return Processor(initialize, lambda o, state: (np.array(o), kappa), nupdate=nupdate)

@@ -601,6 +601,119 @@ def maxabs(u):
 
 
 # --------------------------------------------------------------------------
+# Observers  (src/processors.jl:77-198, 303-332; src/utils.jl:49-108)
+# --------------------------------------------------------------------------
+
+def vorticity(u, setup):
+    """vorticity! src/operators.jl:989-1021 over ndrange N-1 (Julia indices 1..N-1)."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    lo = tuple(slice(0, n - 1) for n in N)
+
+    def sh(b):
+        return tuple(slice(1, n) if a == b else slice(0, n - 1) for a, n in enumerate(N))
+
+    def du(b):  # Delta_u[b][I[b]] for I[b] = 1..N-1
+        return _ax(g.Delta_u[b][: N[b] - 1], b, D)
+
+    if D == 2:
+        w = scalarfield(setup)
+        w[lo] = (u[sh(0) + (1,)] - u[lo + (1,)]) / du(0) - (u[sh(1) + (0,)] - u[lo + (0,)]) / du(1)
+        return w
+    w = vectorfield(setup)
+    for a, ap, am in ((0, 1, 2), (1, 2, 0), (2, 0, 1)):
+        w[lo + (a,)] = (u[sh(ap) + (am,)] - u[lo + (am,)]) / du(ap) - (u[sh(am) + (ap,)] - u[lo + (ap,)]) / du(am)
+    return w
+
+
+def interpolate_u_p(u, setup):
+    """interpolate_u_p! src/operators.jl:1311-1326."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    up = vectorfield(setup)
+    for a in range(D):
+        up[_int(N) + (a,)] = (u[_int(N, _e(D, a, -1)) + (a,)] + u[_int(N) + (a,)]) / T(2)
+    return up
+
+
+def interpolate_w_p(w, setup):
+    """interpolate_w_p! src/operators.jl:1338-1372."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    if D == 2:
+        wp = scalarfield(setup)
+        wp[_int(N)] = (w[_int(N, (-1, -1))] + w[_int(N)]) / T(2)
+        return wp
+    wp = vectorfield(setup)
+    for a in range(D):
+        back = _add(_e(D, (a + 1) % 3, -1), _e(D, (a + 2) % 3, -1))
+        wp[_int(N) + (a,)] = (w[_int(N, back) + (a,)] + w[_int(N) + (a,)]) / T(2)
+    return wp
+
+
+def velocitynorm(up, setup):
+    """observefield(:velocitynorm) src/processors.jl:141-151: sqrt(up1^2 + up2^2 [+ up3^2]), whole array."""
+    D = setup.grid.dimension
+    s = up[..., 0] ** 2 + up[..., 1] ** 2
+    if D == 3:
+        s = s + up[..., 2] ** 2
+    return np.sqrt(s)
+
+
+def observe_vorticity(u, t, setup):
+    """observefield(:vorticity) src/processors.jl:152-155: apply_bc_u!, vorticity!, interpolate_w_p!, restricted to Ip."""
+    u = apply_bc_u(u, t, setup)
+    wp = interpolate_w_p(vorticity(u, setup), setup)
+    return wp[setup.grid.Ip]
+
+
+def spectral_stuff(setup, npoint=100, a=None):
+    """spectral_stuff src/utils.jl:49-108.  Returns 0-based linear (column-major) index lists `inds`, kappa, K."""
+    g = setup.grid
+    D, T, Np = g.dimension, g.T, g.Np
+    a = T((1 + np.sqrt(5)) / 2) if a is None else T(a)
+    K = tuple(n // 2 for n in Np)
+    ks = np.meshgrid(*[np.arange(k, dtype=np.int64) for k in K], indexing="ij")
+    k = np.sqrt(sum(q.astype(np.float64) ** 2 for q in ks)).astype(T)
+    k = k.reshape(-1, order="F")
+    kmax = min(K) - 1
+    isort = np.argsort(k, kind="stable")
+    ksort = k[isort]
+    kappa = np.exp(np.linspace(np.log(1.0), np.log(float(kmax)), npoint))  # logrange(T(1), T(kmax), npoint)
+    kappa = np.array(sorted(set(int(v) for v in np.round(kappa))), dtype=np.int64)
+    inds = []
+    for ki in kappa:
+        if D == 2:
+            lo, hi = T(ki) / a, T(ki) * a
+        else:
+            tol = T(0.01)
+            lo, hi = T(ki) - tol, T(ki) + T(1) - tol
+        js = int(np.searchsorted(ksort, T(lo), side="left"))
+        je = int(np.searchsorted(ksort, T(hi), side="left"))
+        inds.append(isort[js:je])
+    return SimpleNamespace(inds=inds, kappa=kappa, K=K)
+
+
+def observespectrum(u, setup, npoint=100, a=None):
+    """observespectrum src/processors.jl:303-332: per component FFT of u[Ip], |.|^2 / (2 prod(Np)^2) on the
+    first K modes of every axis, summed over components and over the wavenumber shells."""
+    import scipy.fft as sfft
+
+    g = setup.grid
+    D, T, Np = g.dimension, g.T, g.Np
+    st = spectral_stuff(setup, npoint, a)
+    ctype = np.complex64 if T == np.float32 else np.complex128
+    e = None
+    for al in range(D):
+        uhat = sfft.fftn(u[g.Ip + (al,)].astype(ctype))
+        half = uhat[tuple(slice(0, k) for k in st.K)]
+        ea = (half.real ** 2 + half.imag ** 2).astype(T) / T(2 * int(np.prod(Np)) ** 2)
+        e = ea if e is None else e + ea
+    ef = e.reshape(-1, order="F")
+    return np.array([ef[i].sum(dtype=T) for i in st.inds], dtype=T), st.kappa
+
+
+# --------------------------------------------------------------------------
 # Time stepping  (src/time_steppers)
 # --------------------------------------------------------------------------
 
