@@ -80,20 +80,85 @@ def create_spectrum(setup, kp, rng):
     return np.stack([amp * (e[a] / enorm) for a in range(D)], axis=-1).astype(ctype)
 
 
-def random_field(setup, t=0.0, A=1, kp=10, psolver=None, rng=None):
+def create_spectrum_device(setup, kp, rng):
+    """create_spectrum on the device (torch ops on setup.device; same formulas and the same host random stream
+    as `create_spectrum`, so both agree to rounding): returns a complex tensor shaped (D, 2K_D, .., 2K_1)."""
+    import torch
+
+    g = setup.grid
+    D, T = g.dimension, g.T
+    dev, rt = setup.device, setup.tdtype
+    ct = torch.complex64 if T == np.float32 else torch.complex128
+    Nglob = tuple(n + 2 for n in g.n_global)
+    tau = float(T(2 * np.pi))
+    K = tuple(n // 2 for n in g.n_global)
+
+    def ax(v, a):  # Julia axis a (0-based) is torch axis D-1-a of the reversed-shape tensor
+        sh = [1] * D
+        sh[D - 1 - a] = -1
+        return v.reshape(sh)
+
+    def up(x):  # host array in Julia axis order -> device tensor in reversed (C-order) axes
+        return torch.as_tensor(np.ascontiguousarray(np.transpose(x)), device=dev)
+
+    k2 = sum(ax(torch.arange(K[a], device=dev, dtype=rt), a) ** 2 for a in range(D))
+    k = torch.sqrt(k2.expand(tuple(reversed(K))))
+    A = float(T(T(8) * T(tau) / T(3)) / T(kp) ** 5)
+    amp = torch.sqrt(A * k ** 4 * torch.exp(-tau * (k / float(kp)) ** 2)) * float(T(np.prod(Nglob)))
+    xi = [up(rng.random(K).astype(T)) for _ in range(D)]
+    for al in range(D):
+        d = D - 1 - al
+        amp = torch.cat((amp, torch.flip(amp, dims=(d,))), dim=d)
+        xi = [torch.cat((xi[b], torch.flip((-1 if al == b else 1) * xi[b], dims=(d,))), dim=d) for b in range(D)]
+    xis = xi[0]
+    for b in range(1, D):
+        xis = xis + xi[b]
+    amp = torch.polar(amp, tau * xis)
+    KK = tuple(2 * v for v in K)
+    kf = [ax(torch.arange(KK[a], device=dev, dtype=rt), a) for a in range(D)]
+    knorm2 = sum(q ** 2 for q in kf).expand(tuple(reversed(KK)))
+    th = up(rng.random(KK).astype(T))
+    if D == 2:
+        e = [torch.cos(2 * np.pi * th), torch.sin(2 * np.pi * th)]
+    else:
+        ph = up(rng.random(KK).astype(T))
+        e = [torch.sin(np.pi * th) * torch.cos(2 * np.pi * ph), torch.sin(np.pi * th) * torch.sin(2 * np.pi * ph),
+             torch.cos(np.pi * th)]
+    ke = sum(e[a] * kf[a] for a in range(D))
+    zero = (0,) * D
+    for a in range(D):
+        e0 = e[a][zero].clone()
+        e[a] = e[a] - kf[a] * ke / knorm2
+        e[a][zero] = e0
+    enorm = torch.sqrt(sum(q ** 2 for q in e))
+    return torch.stack([amp * (e[a] / enorm).to(ct) for a in range(D)], dim=0)
+
+
+def random_field(setup, t=0.0, A=1, kp=10, psolver=None, rng=None, ondevice=False):
     """random_field(setup, t; A, kp, psolver, rng)  src/initializers.jl:189-219.  The spectrum is
-    generated for the GLOBAL grid on the host (every rank draws the same stream from `rng`), the
-    local slab is cut out, and the projection runs on the device (distributed when nranks > 1)."""
+    generated for the GLOBAL grid (every rank draws the same stream from `rng`), the local slab is cut out,
+    and the projection runs on the device (distributed when nranks > 1).  `ondevice=True` (single rank) also
+    builds the spectrum and takes the inverse FFT on the device (cuFFT through torch.fft, as the reference does
+    through CUDA.jl), so that a 512^3 start field costs seconds instead of a minute of host time."""
     g = setup.grid
     D, T = g.dimension, g.T
     rng = np.random.default_rng(0) if rng is None else rng
-    uhat = create_spectrum(setup, kp, rng)
-    u = sfft.ifftn(uhat, axes=tuple(range(D)))
-    u = (T(A) * u.real).astype(T)
-    u = np.pad(u, [(1, 1)] * D + [(0, 0)], mode="wrap")  # pad_circular (initializers.jl:209)
     b = setup.backend
-    ul = api.local_slab(u, D, b.rank, b.nranks)
-    ud = api.to_device(ul, setup)
+    if ondevice:
+        import torch
+
+        if getattr(b, "nranks", 1) > 1:
+            raise NotImplementedError("ondevice=True builds the whole field on one device")
+        uhat = create_spectrum_device(setup, kp, rng)
+        u = torch.fft.ifftn(uhat, dim=tuple(range(1, D + 1))).real * float(T(A))
+        ud = torch.nn.functional.pad(u.unsqueeze(0), (1, 1) * D, mode="circular").squeeze(0).to(setup.tdtype).contiguous()
+    else:
+        uhat = create_spectrum(setup, kp, rng)
+        u = sfft.ifftn(uhat, axes=tuple(range(D)))
+        u = (T(A) * u.real).astype(T)
+        u = np.pad(u, [(1, 1)] * D + [(0, 0)], mode="wrap")  # pad_circular (initializers.jl:209)
+        ul = api.local_slab(u, D, b.rank, b.nranks)
+        ud = api.to_device(ul, setup)
     api.apply_bc_u_(ud, t, setup)
     api.project_(ud, setup, psolver)
     return api.apply_bc_u_(ud, t, setup)

@@ -219,3 +219,76 @@ def observespectrum(setup, npoint=100, a=None, nupdate=1):
         return out
 
     return Processor(initialize, lambda o, state: (np.array(o), kappa), nupdate=nupdate)
+
+
+# --------------------------------------------------------------------------------------------
+# raw slab checkpoints (restart of long runs, solver.jl:35-46 takes `ustart`, `tlims[1]`; the reference itself
+# only writes VTK through fieldsaver / vtk_writer).  Format: `<stem>.rank<r>of<P>.json` (D, global n, slab range,
+# dtype, t, n) next to `<stem>.rank<r>of<P>.bin`, the rank's field exactly as in memory: reference layout
+# (N1, .., ND_local + 2, D) column-major, ghosts included.  Every rank writes and reads only its own slab.
+# --------------------------------------------------------------------------------------------
+def _ckpt_paths(stem, setup):
+    b = setup.backend
+    r, p = getattr(b, "rank", 0), getattr(b, "nranks", 1)
+    base = f"{stem}.rank{r}of{p}"
+    return base + ".json", base + ".bin"
+
+
+def save_checkpoint(stem, state, setup):
+    """Write the state `(; u, t, n)` of this rank; returns the two file names."""
+    import json
+
+    g = setup.grid
+    jp, bp = _ckpt_paths(stem, setup)
+    u = state.u.detach().cpu().contiguous().numpy()
+    with open(bp, "wb") as f:
+        f.write(u.tobytes())
+    meta = {"format": "insb200-slab-1", "D": g.dimension, "n_global": list(g.n_global), "N_local": list(g.N),
+            "dtype": np.dtype(g.T).name, "t": float(state.t), "n": int(state.n),
+            "rank": getattr(setup.backend, "rank", 0), "nranks": getattr(setup.backend, "nranks", 1),
+            "layout": "column-major (N1,..,ND,D), ghosts included", "bytes": int(u.nbytes)}
+    with open(jp, "w") as f:
+        json.dump(meta, f)
+    return jp, bp
+
+
+def load_checkpoint(stem, setup):
+    """Read this rank's slab back: returns the state `(; u, temp, t, n)` with u on the device."""
+    import json
+    from types import SimpleNamespace
+
+    import torch
+
+    g = setup.grid
+    jp, bp = _ckpt_paths(stem, setup)
+    with open(jp) as f:
+        meta = json.load(f)
+    if (meta["format"] != "insb200-slab-1" or meta["D"] != g.dimension or list(meta["n_global"]) != list(g.n_global)
+            or list(meta["N_local"]) != list(g.N) or meta["dtype"] != np.dtype(g.T).name):
+        raise ValueError(f"checkpoint {jp} does not belong to this setup: {meta}")
+    shape = (g.dimension,) + tuple(reversed(g.N))
+    u = np.fromfile(bp, dtype=g.T)
+    if u.size != int(np.prod(shape)):
+        raise ValueError(f"checkpoint {bp} is truncated")
+    ud = torch.from_numpy(u.reshape(shape)).to(setup.device)
+    return SimpleNamespace(u=ud, temp=None, t=g.T(meta["t"]), n=int(meta["n"]))
+
+
+def checkpointer(setup, stem, nupdate=1):
+    """Processor writing `save_checkpoint(f"{stem}_{n:06d}", state, setup)` every `nupdate` steps (the restart
+    counterpart of fieldsaver, processors.jl:290-300).  `finalize` returns the list of written stems."""
+
+    def initialize(state):
+        written = []
+
+        def on(s):
+            if s.n % nupdate:
+                return
+            name = f"{stem}_{s.n:06d}"
+            save_checkpoint(name, s, setup)
+            written.append(name)
+
+        state.on(on)
+        return written
+
+    return Processor(initialize, nupdate=nupdate)

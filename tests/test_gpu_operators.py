@@ -145,6 +145,23 @@ def test_operator_properties_gpu():
     assert (uh * d)[Ip].sum() <= 0
 
 
+@pytest.mark.parametrize("n,T", [((32, 48), np.float64), ((16, 32, 16), np.float32)], ids=["2d_f64", "3d_f32"])
+def test_random_field_on_device_matches_host_generation(n, T):
+    """random_field (initializers.jl:189-219) with the spectrum and the inverse FFT on the device against the
+    host generation (same random stream) and against the oracle's."""
+    import insb200 as ins
+
+    so, sc = make_pair(n, T)
+    ud = ins.to_host(ins.random_field(sc, kp=4, rng=np.random.default_rng(5), ondevice=True))
+    uh = ins.to_host(ins.random_field(sc, kp=4, rng=np.random.default_rng(5)))
+    uo = o.random_field(so, kp=4, rng=np.random.default_rng(5))
+    tol = 2e-5 if T == np.float32 else 1e-11
+    compare("device vs host generation", ud, uh, tol)
+    compare("device generation vs oracle", ud, uo, tol)
+    div = ins.to_host(ins.divergence(ins.to_device(ud, sc), sc))[so.grid.Ip]
+    assert np.abs(div).max() < (1e-3 if T == np.float32 else 1e-10)
+
+
 def test_error_behaviour():
     """assert_uniform_periodic (src/utils.jl:1-13) and argument validation of the C ABI."""
     import insb200 as ins

@@ -240,3 +240,22 @@ def test_kernel_variants_bit_identical(T, smag):
     for name, (u, ke) in results.items():
         compare(name, u, ref_u, 0, exact=True)
         assert np.array_equal(ke, ref_ke), name
+
+
+def test_checkpoint_restart_is_bit_identical(tmp_path):
+    """A run interrupted by save_checkpoint / load_checkpoint continues exactly as the uninterrupted one."""
+    import insb200 as ins
+
+    so, sc = make_pair((32, 16, 16), np.float32, smag=True)
+    u0 = o.random_field(so, kp=3, rng=np.random.default_rng(4))
+    ref, _ = ins.solve_unsteady(sc, (0.0, 0.008), ins.to_device(u0, sc), dt=1e-3, theta=0.17)
+    stem = str(tmp_path / "run")
+    half, out = ins.solve_unsteady(sc, (0.0, 0.004), ins.to_device(u0, sc), dt=1e-3, theta=0.17,
+                                   processors={"ck": ins.checkpointer(sc, stem, nupdate=4)})
+    assert out["ck"] == [stem + "_000004"]
+    st = ins.load_checkpoint(out["ck"][-1], sc)
+    assert st.n == 4 and abs(float(st.t) - 0.004) < 1e-9
+    rest, _ = ins.solve_unsteady(sc, (float(st.t), 0.008), st.u, dt=1e-3, theta=0.17)
+    assert np.array_equal(ins.to_host(rest.u), ins.to_host(ref.u))
+    with pytest.raises(ValueError):
+        ins.load_checkpoint(out["ck"][-1], make_pair((32, 16, 32), np.float32)[1])
