@@ -127,6 +127,9 @@ struct insb200_ctx {
   void *pcplx2 = nullptr;                               // transposed spectrum / a2a buffers (nranks>1)
   void *ahat[3] = {nullptr, nullptr, nullptr};          // Laplacian symbol per axis (T)
   void *peerS[16] = {nullptr}, *peerB[16] = {nullptr};  // pcplx / pcplx2 of every rank mapped through CUDA IPC
+  struct NeighbourBuf { void *prev = nullptr, *next = nullptr; };  // ring neighbours' mappings of a local buffer
+  std::map<void *, NeighbourBuf> halo_peers;             // registered by register_halo_buffer (halo planes by peer copies)
+  int p2p_halo = 1;                                     // param "p2p_halo": 0 = halo planes over ncclSend/ncclRecv
   std::map<int, std::vector<CUtensorMap>> peer_tmaps;   // k_zsolve_peer descriptors of the peers' spectra, key = COLS*64 + CX
   int p2p_fused = 0;                                    // param "p2p_fused": k_zsolve_peer gathers / scatters the spectrum itself (3-D, needs p2p)
   int nxp = 0;                                          // row pitch (complex words) of the in-slab spectrum, >= nxh

@@ -121,6 +121,22 @@ static int halo_compact(insb200_ctx *c, void *base, int ncomp, int wminus, int w
   const i64 pl = c->cplane, nl = c->nloc[c->last], G = c->G;
   const i64 Gp = c->padded ? c->gp : G;
   if (wminus > G || wplus > Gp || wminus > nl || wplus > nl) INS_FAIL(c, "halo width exceeds the ghost planes");
+  auto hp = c->halo_peers.find(base);
+  if (c->p2p && c->p2p_halo && hp != c->halo_peers.end()) {
+    // registered buffer: the planes go straight into the ring neighbours' ghost planes (copy engines over NVLink,
+    // buffers mapped with CUDA IPC); the 4-byte all-reduce orders them before the consumers on every rank
+    for (int q = 0; q < ncomp; q++) {
+      const i64 co = q * c->ccomp;
+      if (wminus > 0)
+        INS_CUDA(c, cudaMemcpyAsync((T *)hp->second.next + co + (G - wminus) * pl, (T *)base + co + (G + nl - wminus) * pl,
+                                    (size_t)(wminus * pl) * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+      if (wplus > 0)
+        INS_CUDA(c, cudaMemcpyAsync((T *)hp->second.prev + co + (G + nl) * pl, (T *)base + co + G * pl,
+                                    (size_t)(wplus * pl) * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
+    }
+    INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
+    return 0;
+  }
   INS_NCCL(c, ncclGroupStart());
   for (int q = 0; q < ncomp; q++) {
     T *b = (T *)base + q * c->ccomp;
@@ -271,6 +287,10 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
       if (q != c->rank && c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
     }
   }
+  for (auto &kv : c->halo_peers) {
+    if (kv.second.next) cudaIpcCloseMemHandle(kv.second.next);
+    if (kv.second.prev && kv.second.prev != kv.second.next) cudaIpcCloseMemHandle(kv.second.prev);
+  }
   if (c->comm_stream) {
     cudaStreamSynchronize(c->comm_stream);
     for (auto &e : c->pipe_ev) if (e) cudaEventDestroy(e);
@@ -378,6 +398,51 @@ static int setup_p2p(insb200_ctx *c) {
     return 0;
   }
   c->p2p = 1;
+  return 0;
+}
+
+// Map the ring neighbours' copies of a local buffer (same role, same size on every rank) so that halo planes can
+// be copied straight into their ghost planes.  Collective (all ranks, same order); keeps NCCL halos on failure.
+static int register_halo_buffer(insb200_ctx *c, void *base) {
+  if (!c->p2p || !c->p2p_halo || !base || c->halo_peers.count(base)) return 0;
+  struct Rec {
+    cudaIpcMemHandle_t h;
+    int ok, pad[15];
+  };
+  std::vector<Rec> all(c->nranks);
+  Rec mine;
+  memset(&mine, 0, sizeof(mine));
+  mine.ok = cudaIpcGetMemHandle(&mine.h, base) == cudaSuccess;
+  if (!mine.ok) cudaGetLastError();
+  void *dev = nullptr;
+  INS_CUDA(c, cudaMalloc(&dev, sizeof(Rec) * c->nranks));
+  INS_CUDA(c, cudaMemcpyAsync((char *)dev + sizeof(Rec) * c->rank, &mine, sizeof(Rec), cudaMemcpyHostToDevice, c->stream));
+  INS_NCCL(c, ncclAllGather((char *)dev + sizeof(Rec) * c->rank, dev, sizeof(Rec), ncclChar, c->comm, c->stream));
+  INS_CUDA(c, cudaMemcpyAsync(all.data(), dev, sizeof(Rec) * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  int ok = 1;
+  for (int q = 0; q < c->nranks; q++) ok &= all[q].ok;
+  const int prev = (c->rank + c->nranks - 1) % c->nranks, next = (c->rank + 1) % c->nranks;
+  insb200_ctx::NeighbourBuf nb;
+  if (ok) {
+    if (cudaIpcOpenMemHandle(&nb.next, all[next].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { nb.next = nullptr; ok = 0; }
+    if (ok && prev == next) nb.prev = nb.next;
+    else if (ok && cudaIpcOpenMemHandle(&nb.prev, all[prev].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { nb.prev = nullptr; ok = 0; }
+    if (!ok) cudaGetLastError();
+  }
+  int *flag = (int *)c->barbuf;
+  INS_CUDA(c, cudaMemcpyAsync(flag, &ok, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+  INS_NCCL(c, ncclAllReduce(flag, flag, 1, ncclInt, ncclMin, c->comm, c->stream));
+  INS_CUDA(c, cudaMemcpyAsync(&ok, flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
+  INS_CUDA(c, cudaFree(dev));
+  if (!ok) {
+    if (nb.next) cudaIpcCloseMemHandle(nb.next);
+    if (nb.prev && nb.prev != nb.next) cudaIpcCloseMemHandle(nb.prev);
+    c->p2p_halo = 0;  // (collectively) back to NCCL halos for every buffer
+    return 0;
+  }
+  c->halo_peers[base] = nb;
   return 0;
 }
 
@@ -1519,6 +1584,12 @@ static int ensure_rk(insb200_ctx *c, const Tableau &tb, bool smag) {
   INS_TRY(ensure_fft(c));
   for (int b = 0; b < 3; b++) INS_TRY(ensure_vec(c, &c->ubuf[b]));
   for (int j = 0; j < tb.s; j++) if (tb.need[j]) INS_TRY(ensure_vec(c, &c->kbuf[j]));
+  if (c->nranks > 1) {  // halo planes of the stage velocities and of the multiplier by peer copies
+    INS_TRY(dev_alloc(c, &c->preal2, (size_t)c->ccomp * esize(c)));
+    for (int b = 0; b < 3; b++) INS_TRY(register_halo_buffer(c, c->ubuf[b]));
+    INS_TRY(register_halo_buffer(c, c->preal));
+    INS_TRY(register_halo_buffer(c, c->preal2));
+  }
   if (smag && !(c->D == 3 && c->padded && c->variant >= 2)) INS_TRY(ensure_sigma(c));
   return 0;
 }
@@ -1883,6 +1954,7 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   }
   else if (k == "smag_ty") { if (v != 8 && v != 16) INS_FAIL(c, "smag_ty must be 8 or 16"); c->smag_ty = v; }
   else if (k == "smag_zchunk") { if (v < 2) INS_FAIL(c, "smag_zchunk must be >= 2"); c->smag_zchunk = v; }
+  else if (k == "p2p_halo") c->p2p_halo = v != 0;
   else if (k == "p2p_fused") { if (v < 0 || v > 2) INS_FAIL(c, "p2p_fused must be 0, 1 or 2"); c->p2p_fused = v; }
   else if (k == "p2p") {
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
