@@ -157,6 +157,40 @@ int insb200_solve_unsteady_host(insb200_ctx *ctx, void *u_host, double t0, doubl
                                 const double *c, double theta, double *ke_hist, int ke_cap,
                                 int *nsteps_out, double *t_out);
 
+/* ---- temperature equation and the callers next to the path (single rank) ------------- */
+
+/* temperature_equation(; Pr, Ra, Ge, dodissipation, gdir, nondim_type): src/setup.jl:56-86.  The caller forms the
+ * coefficients alpha1..alpha4 and gamma = alpha1/alpha3 in the field type (exactly representable as double);
+ * gdir is the 1-based gravity axis.  Temperature boundary conditions: periodic only. */
+int insb200_set_temperature(insb200_ctx *ctx, double alpha1, double alpha2, double alpha3, double alpha4,
+                            double gamma, int dodissipation, int gdir);
+/* apply_bc_temp!(temp, t, setup), PeriodicBC: src/boundary_conditions.jl:236-246, 338-339 */
+int insb200_apply_bc_temp(insb200_ctx *ctx, void *temp);
+/* convection_diffusion_temp!(c, u, temp, setup): src/operators.jl:711-735 (ADDS to c on Ip) */
+int insb200_convection_diffusion_temp(insb200_ctx *ctx, void *c, const void *u, const void *temp);
+/* dissipation!(diss, diff, u, setup): src/operators.jl:787-808 (diff is overwritten by diffusion!(0, u); ADDS to diss) */
+int insb200_dissipation(insb200_ctx *ctx, void *diss, void *diff, const void *u);
+/* gravity!(F, temp, setup): src/operators.jl:916-931 (ADDS alpha2 * avg(temp) to F[:, gdir] on Iu[gdir]) */
+int insb200_gravity(insb200_ctx *ctx, void *F, const void *temp);
+/* momentum!(F, u, temp, t, setup) with temp !== nothing: src/operators.jl:967-976 (temp may be NULL) */
+int insb200_momentum_temp(insb200_ctx *ctx, void *F, const void *u, const void *temp, double t);
+/* timestep!(::ExplicitRungeKuttaMethod, ...) with the temperature hooks: step_explicit_runge_kutta.jl:4-59
+ * (cache: time_stepper_caches.jl:34-49).  u and temp are advanced in place with valid ghosts; other arguments as
+ * insb200_rk_step.  First version: one kernel per reference kernel on the reference layout (not fused). */
+int insb200_rk_step_temp(insb200_ctx *ctx, void *u, void *temp, double t, double dt, int s, const double *A,
+                         const double *c, double theta, void *p_out);
+int insb200_rk_steps_temp(insb200_ctx *ctx, void *u, void *temp, double *t, double dt, int nsteps, int s,
+                          const double *A, const double *c, double theta);
+/* right_hand_side!(dudt, u, params_ref, t) of the SciML glue: src/sciml.jl:37-49 (u is not modified) */
+int insb200_right_hand_side(insb200_ctx *ctx, void *dudt, const void *u, double t);
+/* Qfield!(Q, u, setup): src/operators.jl:1441-1460 (Ip written) */
+int insb200_qfield(insb200_ctx *ctx, void *Q, const void *u);
+/* dissipation_from_strain!(eps, u, setup): src/operators.jl:819-836 (Ip written; ghosts of u must be valid) */
+int insb200_dissipation_from_strain(insb200_ctx *ctx, void *eps, const void *u);
+/* get_scale_numbers(u, setup): src/operators.jl:1569-1619.  out8 (host) = uavg, epsilon, eta, lambda, Re_lambda,
+ * L, tau, Re_int; synchronises.  Reductions accumulate in double (the reference sums in T). */
+int insb200_scale_numbers(insb200_ctx *ctx, const void *u, double *out8);
+
 /* ---- introspection --------------------------------------------------------------------------- */
 
 /* Algorithmic bytes per cell per RK step of the current configuration (SURVEY.md 8d model:

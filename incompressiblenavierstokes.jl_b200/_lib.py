@@ -56,6 +56,18 @@ PROTOTYPES = {
     "insb200_interpolate_w_p": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_velocitynorm": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_workspace_bytes": (c_ll, [c_void_p]),
+    "insb200_set_temperature": (c_int, [c_void_p, c_double, c_double, c_double, c_double, c_double, c_int, c_int]),
+    "insb200_apply_bc_temp": (c_int, [c_void_p, c_void_p]),
+    "insb200_convection_diffusion_temp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "insb200_dissipation": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "insb200_gravity": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_momentum_temp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_double]),
+    "insb200_rk_step_temp": (c_int, [c_void_p, c_void_p, c_void_p, c_double, c_double, c_int, P(c_double), P(c_double), c_double, c_void_p]),
+    "insb200_rk_steps_temp": (c_int, [c_void_p, c_void_p, c_void_p, P(c_double), c_double, c_int, c_int, P(c_double), P(c_double), c_double]),
+    "insb200_right_hand_side": (c_int, [c_void_p, c_void_p, c_void_p, c_double]),
+    "insb200_qfield": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_dissipation_from_strain": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "insb200_scale_numbers": (c_int, [c_void_p, c_void_p, P(c_double)]),
 }
 
 _lib = None

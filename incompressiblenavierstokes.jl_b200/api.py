@@ -31,6 +31,9 @@ __all__ = [
     "interpolate_w_p", "velocitynorm_", "total_kinetic_energy", "get_cfl_timestep_", "maxabs", "RKMethods", "LMWray3",
     "runge_kutta_method", "ode_method_cache", "create_stepper", "timestep_", "solve_unsteady",
     "solve_unsteady_host", "init_distributed", "local_slab", "gather_slabs",
+    "temperature_equation", "apply_bc_temp_", "apply_bc_temp", "convection_diffusion_temp_", "convection_diffusion_temp",
+    "dissipation_", "dissipation", "gravity_", "gravity", "right_hand_side_", "create_right_hand_side", "Qfield_", "Qfield",
+    "dissipation_from_strain_", "dissipation_from_strain", "get_scale_numbers",
 ]
 
 
@@ -133,9 +136,9 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
         for bc in boundary_conditions:
             if tuple(bc) != ("periodic", "periodic"):
                 raise AssertionError("B200 backend requires periodic boundary conditions.")
-    if temperature is not None:
-        raise NotImplementedError("temperature equation is outside the B200 hot path (SURVEY 8f)")
     backend = backend or B200Backend()
+    if temperature is not None and backend.nranks > 1:
+        raise NotImplementedError("the temperature equation runs on one rank only (SURVEY 8f rank 4)")
     x = tuple(np.asarray(xa) for xa in x)
     T = x[0].dtype.type
     if T not in (np.float32, np.float64):
@@ -173,9 +176,17 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
     )
     setup = SimpleNamespace(grid=grid, boundary_conditions=boundary_conditions, Re=Re, bodyforce=None,
                             issteadybodyforce=False, closure_model=closure_model, backend=backend,
-                            workgroupsize=workgroupsize, temperature=None, ctx=ctx,
+                            workgroupsize=workgroupsize, temperature=temperature, ctx=ctx,
                             device=torch.device("cuda", backend.device),
                             tdtype=torch.float32 if T == np.float32 else torch.float64)
+    if temperature is not None:
+        q = temperature
+        if getattr(q, "boundary_conditions", None) is not None:
+            for bc in q.boundary_conditions:
+                if tuple(bc) != ("periodic", "periodic"):
+                    raise AssertionError("B200 backend requires periodic temperature boundary conditions.")
+        ctx.call("insb200_set_temperature", float(T(q.alpha1)), float(T(q.alpha2)), float(T(q.alpha3)), float(T(q.alpha4)),
+                 float(T(q.gamma)), int(bool(q.dodissipation)), int(q.gdir))
     if bodyforce is not None:
         if not issteadybodyforce:
             raise NotImplementedError("only steady body forces are on the B200 hot path (setup.jl:25-32)")
@@ -271,10 +282,12 @@ def apply_bc_p(p, t, setup):
 
 def momentum_(F, u, temp, t, setup):
     """momentum!(F, u, temp, t, setup)  src/operators.jl:967-976"""
-    if temp is not None:
-        raise NotImplementedError("temperature is outside the B200 hot path")
     _sync_stream(setup)
-    setup.ctx.call("insb200_momentum", _ptr(_check(F, setup, True)), _ptr(_check(u, setup, True)), float(t))
+    if temp is None:
+        setup.ctx.call("insb200_momentum", _ptr(_check(F, setup, True)), _ptr(_check(u, setup, True)), float(t))
+    else:
+        setup.ctx.call("insb200_momentum_temp", _ptr(_check(F, setup, True)), _ptr(_check(u, setup, True)),
+                       _ptr(_check(temp, setup, False)), float(t))
     return F
 
 
@@ -429,6 +442,8 @@ def project(u, setup, psolver=None):
 
 def pressure_(p, u, temp, t, setup, psolver=None, F=None):
     """pressure!(p, u, temp, t, setup; psolver, F)  src/pressure.jl:41-49"""
+    if temp is not None:
+        raise NotImplementedError("pressure! with a temperature field is not on the B200 path yet")
     _sync_stream(setup)
     setup.ctx.call("insb200_pressure", _ptr(_check(p, setup, False)), _ptr(_check(u, setup, True)), float(t))
     return p
@@ -450,6 +465,131 @@ def smagorinsky_closure(setup):
 
     closure.is_smagorinsky = True
     return closure
+
+
+def temperature_equation(Pr, Ra, Ge, dodissipation=True, boundary_conditions=None, gdir=2, nondim_type=1):
+    """temperature_equation(; Pr, Ra, Ge, dodissipation, boundary_conditions, gdir, nondim_type)  src/setup.jl:56-86.
+    The coefficients take the dtype of `Pr` (NumPy scalar arithmetic, like `eltype(Pr)` in the reference)."""
+    T = np.asarray(Pr).dtype.type
+    if T not in (np.float32, np.float64):
+        T = np.float64
+    Pr, Ra, Ge = T(Pr), T(Ra), T(Ge)
+    if nondim_type == 1:      # free fall velocity
+        a1, a2, a3, a4 = np.sqrt(Pr / Ra), T(1), Ge * np.sqrt(Pr / Ra), T(1) / np.sqrt(Pr * Ra)
+    elif nondim_type == 2:    # heat conduction time scale
+        a1, a2, a3, a4 = Pr, Pr * Ra, Ge / Ra, T(1)
+    elif nondim_type == 3:
+        a1, a2, a3, a4 = np.sqrt(Pr * Ge / Ra), Ge, np.sqrt(Pr * Ge / Ra), np.sqrt(Ge / (Pr * Ra))
+    else:
+        raise ValueError("nondim_type must be 1, 2 or 3")
+    a1, a2, a3, a4 = T(a1), T(a2), T(a3), T(a4)
+    return SimpleNamespace(alpha1=a1, alpha2=a2, alpha3=a3, alpha4=a4, gamma=T(a1 / a3), dodissipation=bool(dodissipation),
+                           boundary_conditions=boundary_conditions, gdir=int(gdir))
+
+
+def _need_temperature(setup):
+    if setup.temperature is None:
+        raise ValueError("setup.temperature is nothing: pass temperature=temperature_equation(...) to Setup")
+
+
+def apply_bc_temp_(temp, t, setup):
+    """apply_bc_temp!(temp, t, setup)  src/boundary_conditions.jl:236-246"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_apply_bc_temp", _ptr(_check(temp, setup, False)))
+    return temp
+
+
+def apply_bc_temp(temp, t, setup):
+    return apply_bc_temp_(temp.clone(), t, setup)
+
+
+def convection_diffusion_temp_(c, u, temp, setup):
+    """convection_diffusion_temp!(c, u, temp, setup)  src/operators.jl:711-735 (adds to c)"""
+    _need_temperature(setup)
+    _sync_stream(setup)
+    setup.ctx.call("insb200_convection_diffusion_temp", _ptr(_check(c, setup, False)), _ptr(_check(u, setup, True)),
+                   _ptr(_check(temp, setup, False)))
+    return c
+
+
+def convection_diffusion_temp(u, temp, setup):
+    return convection_diffusion_temp_(scalarfield(setup), u, temp, setup)
+
+
+def dissipation_(diss, diff, u, setup):
+    """dissipation!(diss, diff, u, setup)  src/operators.jl:787-808 (adds to diss; diff is scratch)"""
+    _need_temperature(setup)
+    _sync_stream(setup)
+    setup.ctx.call("insb200_dissipation", _ptr(_check(diss, setup, False)), _ptr(_check(diff, setup, True)),
+                   _ptr(_check(u, setup, True)))
+    return diss
+
+
+def dissipation(u, setup):
+    return dissipation_(scalarfield(setup), vectorfield(setup), u, setup)
+
+
+def gravity_(F, temp, setup):
+    """gravity!(F, temp, setup)  src/operators.jl:916-931 (adds to F)"""
+    _need_temperature(setup)
+    _sync_stream(setup)
+    setup.ctx.call("insb200_gravity", _ptr(_check(F, setup, True)), _ptr(_check(temp, setup, False)))
+    return F
+
+
+def gravity(temp, setup):
+    return gravity_(vectorfield(setup), temp, setup)
+
+
+def right_hand_side_(dudt, u, params_ref, t):
+    """right_hand_side!(dudt, u, params_ref, t)  src/sciml.jl:37-49; params_ref = (setup, psolver)."""
+    setup = params_ref[0]
+    _sync_stream(setup)
+    setup.ctx.call("insb200_right_hand_side", _ptr(_check(dudt, setup, True)), _ptr(_check(u, setup, True)), float(t))
+    return None
+
+
+def create_right_hand_side(setup, psolver=None):
+    """create_right_hand_side(setup, psolver)  src/sciml.jl:13-19: returns f(u, param, t) -> dudt."""
+
+    def right_hand_side(u, param, t):
+        dudt = vectorfield(setup)
+        right_hand_side_(dudt, u, (setup, psolver), t)
+        return dudt
+
+    return right_hand_side
+
+
+def Qfield_(Q, u, setup):
+    """Qfield!(Q, u, setup)  src/operators.jl:1441-1460"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_qfield", _ptr(_check(Q, setup, False)), _ptr(_check(u, setup, True)))
+    return Q
+
+
+def Qfield(u, setup):
+    return Qfield_(scalarfield(setup), u, setup)
+
+
+def dissipation_from_strain_(eps, u, setup):
+    """dissipation_from_strain!(eps, u, setup)  src/operators.jl:819-836"""
+    _sync_stream(setup)
+    setup.ctx.call("insb200_dissipation_from_strain", _ptr(_check(eps, setup, False)), _ptr(_check(u, setup, True)))
+    return eps
+
+
+def dissipation_from_strain(u, setup):
+    return dissipation_from_strain_(scalarfield(setup), u, setup)
+
+
+def get_scale_numbers(u, setup):
+    """get_scale_numbers(u, setup)  src/operators.jl:1569-1619 -> (; uavg, eps, eta, lam, Relam, L, tau, Re_int)"""
+    _sync_stream(setup)
+    out = (C.c_double * 8)()
+    setup.ctx.call("insb200_scale_numbers", _ptr(_check(u, setup, True)), out)
+    T = setup.grid.T
+    names = ("uavg", "eps", "eta", "lam", "Relam", "L", "tau", "Re_int")
+    return SimpleNamespace(**{k: T(v) for k, v in zip(names, out)})
 
 
 def total_kinetic_energy(u, setup):
@@ -599,8 +739,8 @@ def ode_method_cache(method, setup):
 def create_stepper(method, setup, psolver=None, u=None, temp=None, t=0.0, n=0):
     """create_stepper(method; setup, psolver, u, temp, t, n=0)  step_explicit_runge_kutta.jl:1-2"""
     if temp is not None:
-        raise NotImplementedError("temperature is outside the B200 hot path")
-    return SimpleNamespace(setup=setup, psolver=psolver, u=u, temp=None, t=setup.grid.T(t), n=n)
+        _need_temperature(setup)
+    return SimpleNamespace(setup=setup, psolver=psolver, u=u, temp=temp, t=setup.grid.T(t), n=n)
 
 
 def _tableau_args(method):
@@ -627,16 +767,25 @@ def timestep_(method, stepper, dt, theta=None, cache=None, p=None):
     setup = stepper.setup
     s, A, c, keep = _tableau_args(method)
     _sync_stream(setup)
-    setup.ctx.call("insb200_rk_step", _ptr(_check(stepper.u, setup, True)), float(stepper.t), float(dt), s, A, c,
-                   _theta(setup, theta), _ptr(p) if p is not None else None)
+    if stepper.temp is None:
+        setup.ctx.call("insb200_rk_step", _ptr(_check(stepper.u, setup, True)), float(stepper.t), float(dt), s, A, c,
+                       _theta(setup, theta), _ptr(p) if p is not None else None)
+    else:
+        setup.ctx.call("insb200_rk_step_temp", _ptr(_check(stepper.u, setup, True)), _ptr(_check(stepper.temp, setup, False)),
+                       float(stepper.t), float(dt), s, A, c, _theta(setup, theta), _ptr(p) if p is not None else None)
     T = setup.grid.T
     t = T(stepper.t + T(method.c[-1]) * T(dt))
-    return create_stepper(method, setup, stepper.psolver, stepper.u, None, t, stepper.n + 1)
+    return create_stepper(method, setup, stepper.psolver, stepper.u, stepper.temp, t, stepper.n + 1)
 
 
-def _rk_steps(method, setup, u, t, dt, nsteps, theta, ke_hist=False):
+def _rk_steps(method, setup, u, t, dt, nsteps, theta, ke_hist=False, temp=None):
     s, A, c, keep = _tableau_args(method)
     tt = C.c_double(float(t))
+    if temp is not None:
+        _sync_stream(setup)
+        setup.ctx.call("insb200_rk_steps_temp", _ptr(_check(u, setup, True)), _ptr(_check(temp, setup, False)), C.byref(tt),
+                       float(dt), int(nsteps), s, A, c, _theta(setup, theta))
+        return setup.grid.T(tt.value), None
     ke = (C.c_double * (nsteps + 1))() if ke_hist else None
     _sync_stream(setup)
     setup.ctx.call("insb200_rk_steps", _ptr(_check(u, setup, True)), C.byref(tt), float(dt), int(nsteps), s, A, c,
@@ -646,7 +795,7 @@ def _rk_steps(method, setup, u, t, dt, nsteps, theta, ke_hist=False):
 
 def get_state(stepper):
     """get_state(stepper)  src/solver.jl:95-98"""
-    return SimpleNamespace(u=stepper.u, temp=None, t=stepper.t, n=stepper.n)
+    return SimpleNamespace(u=stepper.u, temp=stepper.temp, t=stepper.t, n=stepper.n)
 
 
 def solve_unsteady(setup, tlims, ustart, tempstart=None, method=None, psolver=None, dt=None, dt_min=None,
@@ -658,13 +807,12 @@ def solve_unsteady(setup, tlims, ustart, tempstart=None, method=None, psolver=No
     two processor firings (their `nupdate`) run inside one `insb200_rk_steps` call, i.e. without
     touching the reference layout or the host."""
     T = setup.grid.T
-    if tempstart is not None:
-        raise NotImplementedError("temperature is outside the B200 hot path")
     method = method or RKMethods.RK44(T=T)
     psolver = psolver or default_psolver(setup)
     u = ustart.clone() if docopy else ustart
+    temp = None if tempstart is None else (tempstart.clone() if docopy else tempstart)
     tstart, tend = T(tlims[0]), T(tlims[1])
-    stepper = create_stepper(method, setup, psolver, u, None, tstart)
+    stepper = create_stepper(method, setup, psolver, u, temp, tstart)
     processors = processors or {}
     state = Observable(get_state(stepper))
     initialized = {k: v.initialize(state) for k, v in processors.items()}
@@ -687,12 +835,12 @@ def solve_unsteady(setup, tlims, ustart, tempstart=None, method=None, psolver=No
         it = 0
         while it < nstep:
             m = min(chunk, nstep - it)
-            t, _ = _rk_steps(method, setup, stepper.u, stepper.t, d, m, theta)
+            t, _ = _rk_steps(method, setup, stepper.u, stepper.t, d, m, theta, temp=stepper.temp)
             it += m
-            stepper = create_stepper(method, setup, psolver, stepper.u, None, t, stepper.n + m)
+            stepper = create_stepper(method, setup, psolver, stepper.u, stepper.temp, t, stepper.n + m)
             state.set(get_state(stepper))
     outputs = {k: processors[k].finalize(initialized[k], state) for k in processors}
-    return SimpleNamespace(u=stepper.u, temp=None, t=stepper.t, n=stepper.n), outputs
+    return SimpleNamespace(u=stepper.u, temp=stepper.temp, t=stepper.t, n=stepper.n), outputs
 
 
 def solve_unsteady_host(setup, tlims, ustart_host, method=None, dt=None, cfl=0.9, n_adapt_dt=1, theta=None,

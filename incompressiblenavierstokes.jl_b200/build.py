@@ -12,7 +12,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libinsb200.so")
-SOURCES = [os.path.join(CSRC, "insb200.cu")]
+SOURCES = [os.path.join(CSRC, "insb200.cu"), os.path.join(CSRC, "temperature.cu")]
+OBJDIR = os.path.join(HERE, "build")  # git-ignored object cache: only stale translation units are recompiled
 HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "zsolve.cuh")] + [
     os.path.join(os.path.dirname(HERE), "include", "insb200.h")
 ]
@@ -21,7 +22,7 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-lineinfo", "-O3", "-std=c++17",
     "-fmad=false",                      # arithmetic contract of stencil.cuh: no FMA contraction
-    "-Xcompiler", "-fPIC", "-shared",
+    "-Xcompiler", "-fPIC",
 ]
 
 
@@ -38,29 +39,53 @@ def _rpaths():
     return paths
 
 
-def needs_build():
-    if not os.path.exists(LIB):
+def _stale(target, deps):
+    if not os.path.exists(target):
         return True
-    t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(f) > t for f in SOURCES + HEADERS + [os.path.abspath(__file__)])
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(f) > t for f in deps)
+
+
+def needs_build():
+    return _stale(LIB, SOURCES + HEADERS + [os.path.abspath(__file__)])
 
 
 def build(force=False, verbose=False, extra_flags=()):
     if not force and not needs_build():
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)
+    os.makedirs(OBJDIR, exist_ok=True)
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-o", LIB] + SOURCES + ["-lcufft", "-lnccl"]
+    # one nvcc -c per translation unit (run concurrently), then one link
+    jobs, objs = [], []
+    for src in SOURCES:
+        obj = os.path.join(OBJDIR, os.path.splitext(os.path.basename(src))[0] + ".o")
+        objs.append(obj)
+        if not force and not extra_flags and not _stale(obj, [src] + HEADERS + [os.path.abspath(__file__)]):
+            continue
+        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-c", "-o", obj, src]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+            print(" ".join(cmd))
+        jobs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = []
+    for src, pr in jobs:
+        out, _ = pr.communicate()
+        if verbose:
+            print(out)
+        if pr.returncode != 0:
+            failed.append("nvcc failed on " + src + ":\n" + out)
+    if failed:
+        raise RuntimeError("\n".join(failed))
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-Xcompiler", "-fPIC", "-o", LIB] + objs + ["-lcufft", "-lnccl"]
     for p in _rpaths():
         cmd += ["-Xlinker", "-rpath=" + p]
-    if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-        print(" ".join(cmd))
     res = subprocess.run(cmd, capture_output=True, text=True)
     if verbose:
+        print(" ".join(cmd))
         print(res.stdout, res.stderr)
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+        raise RuntimeError("link failed:\n" + res.stdout + res.stderr)
     return LIB
 
 

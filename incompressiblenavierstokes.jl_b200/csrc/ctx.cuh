@@ -147,6 +147,12 @@ struct insb200_ctx {
   bool rk_alloc = false;
   int rk_nk = 0;
 
+  // temperature equation (temperature.cu): coefficients of temperature_equation (setup.jl:56-86) and the
+  // reference-layout RK cache (ustart, ku, tempstart, ktemp, diff, p) of the temperature stepper
+  struct TempEq { bool set = false; double a1 = 0, a2 = 0, a3 = 0, a4 = 0, gamma = 1; int dodissipation = 1; int gdir = 1; } tq;
+  void *tws = nullptr;
+  size_t tws_bytes = 0;
+
   // FFT plans
   cufftHandle plan_fwd = 0, plan_inv = 0;               // nranks==1: D-dim R2C / C2R
   cufftHandle plan_fwd_in = 0, plan_inv_in = 0;         // nranks>1: in-slab transforms

@@ -301,7 +301,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio, c->ztw};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio, c->ztw, c->tws};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }

@@ -101,14 +101,16 @@ def energy_history(setup, nupdate=1):
     return Processor(initialize, lambda pts, state: np.array(pts), nupdate=nupdate)
 
 
-def observefield(setup, fieldname, nupdate=1, psolver=None):
-    """observefield(state; setup, fieldname)  src/processors.jl:77-198 for `1 | 2 | 3` (one interpolated
-    velocity component), `:velocity`, `:velocitynorm`, `:vorticity`, `:pressure` -- all computed on the device
-    by the library -- and `:velocity_raw` (u[Ip, :] as stored).  Returns host arrays restricted to Ip."""
+def observefield(setup, fieldname, nupdate=1, psolver=None, logtol=None):
+    """observefield(state; setup, fieldname, logtol)  src/processors.jl:77-198 for `1 | 2 | 3` (one interpolated
+    velocity component), `:velocity`, `:velocitynorm`, `:vorticity`, `:pressure`, `:Qfield`, `:temperature` -- all
+    computed on the device by the library -- and `:velocity_raw` (u[Ip, :] as stored).  Returns host arrays
+    restricted to Ip."""
     g = setup.grid
     D = g.dimension
-    if fieldname not in (1, 2, 3, "velocity", "velocitynorm", "vorticity", "pressure", "velocity_raw"):
+    if fieldname not in (1, 2, 3, "velocity", "velocitynorm", "vorticity", "pressure", "velocity_raw", "Qfield", "temperature"):
         raise ValueError("Unknown fieldname")  # processors.jl:128
+    logtol = np.finfo(g.T).eps if logtol is None else logtol  # processors.jl:81
     if fieldname in (1, 2, 3) and fieldname > D:
         raise ValueError("Unknown fieldname")
 
@@ -126,6 +128,11 @@ def observefield(setup, fieldname, nupdate=1, psolver=None):
                 f = api.to_host(api.pressure(s.u, None, s.t, setup, psolver))[g.Ip]
             elif fieldname == "velocity_raw":
                 f = api.to_host(s.u)[g.Ip]
+            elif fieldname == "temperature":
+                f = api.to_host(s.temp)[g.Ip]
+            elif fieldname == "Qfield":  # processors.jl:172-176: Qfield!, then `@. Qin = log(max(logtol, Qin))` (device broadcast)
+                Q = api.Qfield(s.u, setup)
+                f = api.to_host(Q.clamp_min_(float(logtol)).log_())[g.Ip]
             elif fieldname in (1, 2, 3):
                 f = api.to_host(api.interpolate_u_p_(up, s.u, setup))[g.Ip + (fieldname - 1,)]
             elif fieldname == "velocity":

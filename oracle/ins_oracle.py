@@ -116,7 +116,7 @@ def Grid(x):
     )
 
 
-def Setup(x, Re=None, bodyforce=None, issteadybodyforce=True, closure_model=None):
+def Setup(x, Re=None, bodyforce=None, issteadybodyforce=True, closure_model=None, temperature=None):
     """`Setup(; x, Re, bodyforce, issteadybodyforce, closure_model)` src/setup.jl:2-46.
 
     Only periodic boundary conditions (the hot path's admissible domain,
@@ -127,7 +127,7 @@ def Setup(x, Re=None, bodyforce=None, issteadybodyforce=True, closure_model=None
     Re = T(1000) if Re is None else T(Re)
     setup = SimpleNamespace(
         grid=grid, Re=Re, bodyforce=bodyforce, issteadybodyforce=False,
-        closure_model=closure_model, temperature=None,
+        closure_model=closure_model, temperature=temperature,
     )
     if bodyforce is not None and issteadybodyforce:
         # setup.jl:25-32: materialise the steady force once as a vector field
@@ -391,6 +391,99 @@ def momentum(u, temp, t, setup):
     F = convectiondiffusion(u, setup)
     if setup.bodyforce is not None:
         F = applybodyforce(F, u, t, setup)
+    if temp is not None:
+        F = gravity(F, temp, setup)
+    return F
+
+
+# Temperature equation ------------------------------------------------------
+
+def temperature_equation(Pr, Ra, Ge, dodissipation=True, gdir=2, nondim_type=1):
+    """temperature_equation src/setup.jl:56-86 (periodic temperature boundary conditions only).
+    `gdir` is 1-based like the reference; the coefficients carry the dtype of `Pr`."""
+    T = np.asarray(Pr).dtype.type
+    Pr, Ra, Ge = T(Pr), T(Ra), T(Ge)
+    if nondim_type == 1:
+        a1 = np.sqrt(Pr / Ra)
+        a2 = T(1)
+        a3 = Ge * np.sqrt(Pr / Ra)
+        a4 = T(1) / np.sqrt(Pr * Ra)
+    elif nondim_type == 2:
+        a1 = Pr
+        a2 = Pr * Ra
+        a3 = Ge / Ra
+        a4 = T(1)
+    elif nondim_type == 3:
+        a1 = np.sqrt(Pr * Ge / Ra)
+        a2 = Ge
+        a3 = np.sqrt(Pr * Ge / Ra)
+        a4 = np.sqrt(Ge / (Pr * Ra))
+    else:
+        raise ValueError("nondim_type must be 1, 2 or 3")
+    a1, a2, a3, a4 = T(a1), T(a2), T(a3), T(a4)
+    return SimpleNamespace(alpha1=a1, alpha2=a2, alpha3=a3, alpha4=a4, gamma=T(a1 / a3),
+                           dodissipation=bool(dodissipation), gdir=int(gdir))
+
+
+def apply_bc_temp(temp, t, setup, copy=True):
+    """apply_bc_temp! src/boundary_conditions.jl:236-246; PeriodicBC -> apply_bc_p! (:338-339)."""
+    return apply_bc_p(temp, t, setup, copy=copy)
+
+
+def _avg(phi, setup, b, shift=None):
+    """avg(phi, Delta, I + shift, b) src/operators.jl:59-62 for I in Ip:
+    (D[b][I[b]+1]*phi[I] + D[b][I[b]]*phi[I+e_b]) / (D[b][I[b]] + D[b][I[b]+1])."""
+    g = setup.grid
+    D, N = g.dimension, g.N
+    shift = (0,) * D if shift is None else shift
+    d0 = _m1(N, b, g.Delta[b], shift[b])
+    d1 = _m1(N, b, g.Delta[b], shift[b] + 1)
+    return (d1 * phi[_int(N, shift)] + d0 * phi[_int(N, _add(shift, _e(D, b)))]) / (d0 + d1)
+
+
+def convection_diffusion_temp(c, u, temp, setup):
+    """convection_diffusion_temp! src/operators.jl:711-735 (adds to `c`, returns the new array)."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    a4 = setup.temperature.alpha4
+    cI = np.zeros(g.Np, dtype=T)
+    for b in range(D):
+        eb, mb = _e(D, b), _e(D, b, -1)
+        dTdx1 = (temp[_int(N)] - temp[_int(N, mb)]) / _m1(N, b, g.Delta_u[b], -1)
+        dTdx2 = (temp[_int(N, eb)] - temp[_int(N)]) / _m1(N, b, g.Delta_u[b])
+        uT1 = u[_int(N, mb) + (b,)] * _avg(temp, setup, b, mb)
+        uT2 = u[_int(N) + (b,)] * _avg(temp, setup, b)
+        cI = cI + (-(uT2 - uT1) + a4 * (dTdx2 - dTdx1)) / _m1(N, b, g.Delta[b])
+    c = c.copy(order="F")
+    c[g.Ip] = c[g.Ip] + cI
+    return c
+
+
+def dissipation(diss, u, setup):
+    """dissipation! src/operators.jl:787-808: diff = diffusion!(zeros, u) (its ghosts stay 0), then
+    diss[I] += sum_b Re*a1/gamma * (u[I-e_b,b]*diff[I-e_b,b] + u[I,b]*diff[I,b]) / 2."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    tq = setup.temperature
+    diff = diffusion(u, setup)
+    d = np.zeros(g.Np, dtype=T)
+    coef = setup.Re * tq.alpha1 / tq.gamma
+    for b in range(D):
+        mb = _e(D, b, -1)
+        d = d + coef * (u[_int(N, mb) + (b,)] * diff[_int(N, mb) + (b,)] + u[_int(N) + (b,)] * diff[_int(N) + (b,)]) / T(2)
+    diss = diss.copy(order="F")
+    diss[g.Ip] = diss[g.Ip] + d
+    return diss
+
+
+def gravity(F, temp, setup):
+    """gravity! src/operators.jl:916-931: F[I, gdir] += alpha2 * avg(temp, Delta, I, gdir) on Iu[gdir]."""
+    g = setup.grid
+    N = g.N
+    tq = setup.temperature
+    gd = tq.gdir - 1
+    F = F.copy(order="F")
+    F[_int(N) + (gd,)] = F[_int(N) + (gd,)] + tq.alpha2 * _avg(temp, setup, gd)
     return F
 
 
@@ -713,6 +806,83 @@ def observespectrum(u, setup, npoint=100, a=None):
     return np.array([ef[i].sum(dtype=T) for i in st.inds], dtype=T), st.kappa
 
 
+def strain_gradient(u, setup):
+    """`grad(u, I, D, Du)` src/operators.jl:1072-1088 on all I in Ip: G[a][b] = d_b u_a."""
+    D = setup.grid.dimension
+    return [[_dx(u, setup, a, b) for b in range(D)] for a in range(D)]
+
+
+def dissipation_from_strain(u, setup):
+    """dissipation_from_strain! src/operators.jl:819-836: eps[I] = 2 visc sum(S .* S), S = (G + G')/2."""
+    g = setup.grid
+    D, T = g.dimension, g.T
+    G = strain_gradient(u, setup)
+    ss = None
+    for b in range(D):
+        for a in range(D):
+            S = (G[a][b] + G[b][a]) / T(2)
+            term = S * S
+            ss = term if ss is None else ss + term
+    eps = scalarfield(setup)
+    eps[g.Ip] = T(2) * (T(1) / setup.Re) * ss
+    return eps
+
+
+def Qfield(u, setup):
+    """Qfield! src/operators.jl:1441-1460: Q[I] = -sum_{a,b} (d_b u_a)(d_a u_b) / 2 with one-sided differences
+    (u[I,a]-u[I-e_b,a])/D[b] * (u[I,b]-u[I-e_a,b])/D[a] / 2, accumulated a outer, b inner."""
+    g = setup.grid
+    D, N, T = g.dimension, g.N, g.T
+    q = np.zeros(g.Np, dtype=T)
+    for a in range(D):
+        for b in range(D):
+            q = q - (u[_int(N) + (a,)] - u[_int(N, _e(D, b, -1)) + (a,)]) / _m1(N, b, g.Delta[b]) * (
+                u[_int(N) + (b,)] - u[_int(N, _e(D, a, -1)) + (b,)]) / _m1(N, a, g.Delta[a]) / T(2)
+    Q = scalarfield(setup)
+    Q[g.Ip] = q
+    return Q
+
+
+def get_scale_numbers(u, setup):
+    """get_scale_numbers src/operators.jl:1569-1619, statement by statement.  Note that `field = @. u^2 * Omega_u`
+    (:1582-1583) runs over ALL components for every alpha, so uavg^2 is D times the volume mean of |u|^2."""
+    g = setup.grid
+    D, N, T, Np = g.dimension, g.N, g.T, g.Np
+    visc = T(1) / setup.Re
+    omega = scalewithvolume(np.ones(N, dtype=T, order="F"), setup)
+    acc = T(0)
+    for a in range(D):
+        om_u = None
+        for b in range(D):
+            v = _ax(g.Delta_u[b] if a == b else g.Delta[b], b, D)
+            om_u = v if om_u is None else om_u * v
+        field = u ** 2 * om_u[..., None]
+        acc = acc + field[g.Iu[0]].sum(dtype=T) / np.broadcast_to(om_u, N)[g.Iu[0]].sum(dtype=T)
+    uavg = T(np.sqrt(acc))
+    eps = dissipation_from_strain(u, setup)
+    eps = T((omega * eps)[g.Ip].sum(dtype=T) / omega[g.Ip].sum(dtype=T))
+    eta = T((visc ** 3 / eps) ** T(0.25))
+    lam = T(np.sqrt(T(5) * visc / eps) * uavg)
+    Relam = T(lam * uavg / np.sqrt(T(3)) / visc)
+    K = tuple(n // 2 for n in Np)
+    ctype = np.complex64 if T == np.float32 else np.complex128
+    e = None
+    ks = np.meshgrid(*[np.arange(k, dtype=np.float64) for k in K], indexing="ij")
+    knorm = np.sqrt(sum(q ** 2 for q in ks)).astype(T)
+    for a in range(D):
+        uhat = sfft.fftn(u[g.Ip + (a,)].astype(ctype))
+        half = uhat[tuple(slice(0, k) for k in K)]
+        ea = (half.real ** 2 + half.imag ** 2).astype(T) / T(2 * int(np.prod(Np)) ** 2)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            ea = ea / knorm
+        e = ea if e is None else e + ea
+    e[(0,) * D] = 0
+    L = T(T(3 * np.pi) / T(2) / uavg ** 2 * e.sum(dtype=T))
+    tau = T(L / uavg)
+    Re_int = T(L * uavg / visc)
+    return SimpleNamespace(uavg=uavg, eps=eps, eta=eta, lam=lam, Relam=Relam, L=L, tau=tau, Re_int=Re_int)
+
+
 # --------------------------------------------------------------------------
 # Time stepping  (src/time_steppers)
 # --------------------------------------------------------------------------
@@ -809,6 +979,7 @@ def create_stepper(method, setup, psolver, u, temp=None, t=0.0, n=0):
 def timestep(method, stepper, dt, theta=None, return_p=False):
     """timestep!(::ExplicitRungeKuttaMethod, ...) src/time_steppers/step_explicit_runge_kutta.jl:4-59."""
     setup, psolver, u, t, n = stepper.setup, stepper.psolver, stepper.u, stepper.t, stepper.n
+    temp = getattr(stepper, "temp", None)
     T = setup.grid.T
     dt = T(dt)
     A, b, c = method.A, method.b, method.c
@@ -816,11 +987,19 @@ def timestep(method, stepper, dt, theta=None, return_p=False):
     m = setup.closure_model
     tstart = t
     ustart = u.copy(order="F")
-    ku = []
+    tempstart = None if temp is None else temp.copy(order="F")
+    ku, ktemp = [], []
     p = None
     for i in range(nstage):
         u = apply_bc_u(u, t, setup, copy=False)
-        k = momentum(u, None, t, setup)
+        if temp is not None:
+            temp = apply_bc_temp(temp, t, setup, copy=False)
+        k = momentum(u, temp, t, setup)
+        if temp is not None:
+            kt = convection_diffusion_temp(scalarfield(setup), u, temp, setup)   # :23-24
+            if setup.temperature.dodissipation:
+                kt = dissipation(kt, u, setup)                                    # :25
+            ktemp.append(kt)
         if m is not None:
             k = k + m(u, theta)
         ku.append(k)
@@ -828,11 +1007,26 @@ def timestep(method, stepper, dt, theta=None, return_p=False):
         u = ustart.copy(order="F")
         for j in range(i + 1):
             u = u + T(dt * A[i, j]) * ku[j]
+        if temp is not None:
+            temp = tempstart.copy(order="F")
+            for j in range(i + 1):
+                temp = temp + T(dt * A[i, j]) * ktemp[j]
         u = apply_bc_u(u, t, setup, copy=False)
         u, p = project(u, setup, psolver, return_p=True)
     u = apply_bc_u(u, t, setup, copy=False)
-    out = create_stepper(method, setup, psolver, u, None, t, n + 1)
+    if temp is not None:
+        temp = apply_bc_temp(temp, t, setup, copy=False)
+    out = create_stepper(method, setup, psolver, u, temp, t, n + 1)
     return (out, p) if return_p else out
+
+
+def right_hand_side(u, t, setup, psolver):
+    """right_hand_side! src/sciml.jl:37-49 (== create_right_hand_side :13-19): apply_bc_u!(copy(u)),
+    momentum!, apply_bc_u!(dudt; dudt=true) (periodic: ghost fill), project!."""
+    v = apply_bc_u(u, t, setup)
+    F = momentum(v, None, t, setup)
+    F = apply_bc_u(F, t, setup, copy=False)
+    return project(F, setup, psolver)
 
 
 def solve_unsteady(setup, tlims, ustart, method=None, psolver=None, dt=None, dt_min=None,
