@@ -89,10 +89,13 @@ struct insb200_ctx {
   int fft_chunk = 0;       // param: planes per in-plane cuFFT exec (0 = the whole slab); small chunks keep the x->y intermediate in L2
   int fft_batch = 0;       // planes per exec of plan_fwd_in / plan_inv_in as planned
   long long fft_cdist = 0; // complex words between consecutive planes of the in-slab spectrum
+  int stage_x2 = 0;        // F32 stage kernel: 0 = k_stage3d_tma (default: fastest overall); two cells per thread on packed FP32 (k_stage3d_tma_x2): 1 = exact, 2 = FFMA2-contracted
   int smag_v = 2;          // closure kernel: 1 = shared-memory stencil (k_smag3d_tma), 2 = register-carried (k_smag3d_v2)
   int smag_ty = 16;        // tile height of k_smag3d_v2: 16 (one 640-thread block per SM) or 8 (two 384-thread blocks)
-  int smag_zchunk = 128;   // planes marched per block of k_smag3d_v2
-  int zchunk = 64;         // tiled stage kernel: planes marched per block
+  int smag_zchunk = 0;     // planes marched per block of k_smag3d_v2 (0 = automatic, auto_zchunk)
+  int zchunk = 0;          // stage kernels: planes marched per block (0 = automatic for the TMA kernels, 64 for the LDG-tiled ones)
+  int nsm = 148;           // SMs of the device
+  int rows2d = 1;          // 2-D: divergence / gradient kernels march several rows per thread (0 = one cell per thread)
   int padded = 0;          // 1: padded layout with real ghost cells (3-D)
   int org[3] = {0, 0, 0};  // interior origin inside the padded box (elements)
   int ext[3] = {1, 1, 1};  // padded extents PX, PY, PZ

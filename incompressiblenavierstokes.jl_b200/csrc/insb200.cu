@@ -11,6 +11,7 @@
 #include "stencil.cuh"
 #include "tiled.cuh"
 #include "tma_stage.cuh"
+#include "tma_stage_x2.cuh"
 #include "zsolve.cuh"
 
 namespace insb200 {
@@ -253,6 +254,7 @@ extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype,
   if (cudaSetDevice(device) != cudaSuccess) { c->err = "cudaSetDevice failed"; return bail(1); }
   if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) { c->err = "stream creation failed"; return bail(1); }
   c->stream = c->own_stream;
+  if (cudaDeviceGetAttribute(&c->nsm, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || c->nsm < 1) c->nsm = 148;
   if (nranks > 1) {
     ncclUniqueId id;
     memcpy(&id, nccl_id, sizeof id);
@@ -1101,6 +1103,15 @@ static int op_smagorinsky(insb200_ctx *c, void *s, const void *u, double theta) 
 template <typename T, int D>
 static int launch_divergence(insb200_ctx *c, View<T> out, View<const T> u, Geo g, bool scale) {
   ScopedTimer tm(c, TM_DIVERGENCE);
+  if constexpr (D == 2) {
+    if (c->rows2d) {
+      constexpr int RPT = 4;
+      dim3 grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 4 * RPT - 1) / (4 * RPT), 1);
+      k_divergence_y<T, RPT><<<grd, cell_block(), 0, c->stream>>>(out, u, g, make_rh<T>(c), volume<T>(c), scale ? 1 : 0);
+      CHECK_LAUNCH(c);
+      return 0;
+    }
+  }
   k_divergence<T, D><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(out, u, g, make_rh<T>(c), volume<T>(c), scale ? 1 : 0);
   CHECK_LAUNCH(c);
   return 0;
@@ -1154,6 +1165,10 @@ static int launch_gradient(insb200_ctx *c, View<T> out, View<const T> p, Geo gp)
     constexpr int ZPT = 4;
     dim3 grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 3) / 4, (c->nloc[2] + ZPT - 1) / ZPT);
     k_gradient_z<T, MODE, ZPT><<<grd, cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
+  } else if (c->rows2d) {
+    constexpr int RPT = 4;
+    dim3 grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 4 * RPT - 1) / (4 * RPT), 1);
+    k_gradient_y<T, MODE, RPT><<<grd, cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
   } else
   k_gradient<T, D, MODE><<<cell_grid(c->nloc), cell_block(), 0, c->stream>>>(out, p, gp, make_rh<T>(c));
   CHECK_LAUNCH(c);
@@ -1408,7 +1423,7 @@ static int launch_stage3d(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, 
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = true;
   }
-  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  const int zc = std::max(2, std::min(c->zchunk > 0 ? c->zchunk : 64, c->nloc[2]));
   dim3 grd(c->nloc[0] / TX, c->nloc[1] / TY, (c->nloc[2] + zc - 1) / zc), blk(TX, TY, 1);
   kern<<<grd, blk, smem, c->stream>>>(a, g, visc, rh, volume<T>(c), zc);
   CHECK_LAUNCH(c);
@@ -1430,7 +1445,7 @@ static int launch_stage_tiled(insb200_ctx *c, const StageArgs<T> &a, Geo g, T vi
 template <typename T>
 static int launch_divergence_planes(insb200_ctx *c, T *out, const T *u, Geo g) {
   ScopedTimer tm(c, TM_DIVERGENCE);
-  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  const int zc = std::max(2, std::min(c->zchunk > 0 ? c->zchunk : 64, c->nloc[2]));
   dim3 blk(64, 4, 1), grd((c->nloc[0] + 63) / 64, (c->nloc[1] + 3) / 4, (c->nloc[2] + zc - 1) / zc);
   k_divergence_planes<T><<<grd, blk, 0, c->stream>>>(out, u, c->csy, c->csz, c->ccomp, g, make_rh<T>(c), volume<T>(c), zc);
   CHECK_LAUNCH(c);
@@ -1449,6 +1464,25 @@ static bool tma_supported(const insb200_ctx *c) {
 
 static const int kNS = 5;  // velocity plane slots of the stage kernel (prefetch distance 2 planes)
 
+// Planes marched per block of a z-marching kernel.  `user` > 0: the value set through insb200_set_param.  Otherwise
+// pick the chunk that minimises  rounds x (zc + extra)  with rounds = ceil(tiles x chunks / (SMs x blocks per SM)):
+// a block costs zc planes plus `extra` planes of pipeline prologue, and the grid runs in rounds of resident blocks.
+// Measured against a sweep (tools/sweep_zchunk.sh): 128^3 Float64 stage kernel 64 planes -> 32: 0.112 -> 0.063 ms
+// (64 blocks left 84 of 148 SMs idle); 512^3 closure kernel 128 -> 256: 1.89 -> 1.86 ms.
+static int auto_zchunk(const insb200_ctx *c, int user, int tiles, int blocks_per_sm, int extra) {
+  const int nz = c->nloc[2];
+  if (user > 0) return std::max(2, std::min(user, nz));
+  int best = nz;
+  double best_cost = 1e300;
+  for (int m = 1; m <= std::max(1, nz / 8); m++) {
+    const int zc = (nz + m - 1) / m, chunks = (nz + zc - 1) / zc;
+    const double rounds = std::ceil((double)tiles * chunks / ((double)std::max(1, c->nsm) * blocks_per_sm));
+    const double cost = rounds * (zc + extra);
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = zc; }
+  }
+  return std::max(2, best);
+}
+
 template <typename T, bool PG, bool SA, bool GEN>
 static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T visc, Rh<T> rh, const void *ubase,
                               const void *pbase) {
@@ -1456,14 +1490,28 @@ static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T
   CUtensorMap tu, tp;
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 3, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 4, &tp));
+  const int zc = auto_zchunk(c, c->zchunk, (c->nloc[0] / kTX) * (c->nloc[1] / kTY), sizeof(T) == 4 ? 2 : 1, 4);
+  dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
+  if constexpr (std::is_same<T, float>::value) if (c->stage_x2) {  // two cells per thread on packed FP32 (tma_stage_x2.cuh)
+    auto kex = k_stage3d_tma_x2<f2t<true>, PG, SA, GEN, kTX, kTY, kNS>;    // 1: exact (bit-identical to the scalar kernel)
+    auto kfu = k_stage3d_tma_x2<f2t<false>, PG, SA, GEN, kTX, kTY, kNS>;   // 2: products contracted into FFMA2
+    static bool attr2_set = false;
+    if (!attr2_set) {
+      INS_CUDA(c, cudaFuncSetAttribute(kex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+      INS_CUDA(c, cudaFuncSetAttribute(kfu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+      attr2_set = true;
+    }
+    (c->stage_x2 == 1 ? kex : kfu)<<<grd, dim3(kTX, kTY / 2, 1), Cfg::SMEM, c->stream>>>(tu, tp, a, g, visc, rh, volume<T>(c), zc, c->org[0],
+                                                                                       c->org[1], c->org[2]);
+    CHECK_LAUNCH(c);
+    return 0;
+  }
   auto kern = k_stage3d_tma<T, PG, SA, GEN, kTX, kTY, kNS>;
   static bool attr_set = false;
   if (!attr_set) {
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
     attr_set = true;
   }
-  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
-  dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
   kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, a, g, visc, rh, volume<T>(c), zc, c->org[0], c->org[1], c->org[2]);
   CHECK_LAUNCH(c);
   return 0;
@@ -1489,7 +1537,8 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
   INS_TRY(get_tmap(c, ubase, 3, Cfg::Pipe::BX, kTY + 4, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 5, &tp));
   if constexpr (sizeof(T) == 4) if (c->smag_v >= 2) {  // register-carried z-march (F32)
-    const int zc2 = std::max(2, std::min(c->smag_zchunk, c->nloc[2]));
+    const int ty2 = (c->smag_ty == 8 && c->nloc[1] % 8 == 0) ? 8 : kTY;
+    const int zc2 = auto_zchunk(c, c->smag_zchunk, (c->nloc[0] / kTX) * (c->nloc[1] / ty2), ty2 == 8 ? 2 : 1, 5);
     if (c->smag_ty == 8 && c->nloc[1] % 8 == 0) {  // two blocks of 32 x 12 threads per SM
       typedef Smag2Cfg<T, PG, kTX, 8> Cfg2;
       CUtensorMap tu8, tp8;
@@ -1527,7 +1576,7 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
     INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
     attr_set = true;
   }
-  const int zc = std::max(2, std::min(c->zchunk, c->nloc[2]));
+  const int zc = auto_zchunk(c, c->zchunk, (c->nloc[0] / kTX) * (c->nloc[1] / kTY), sizeof(T) == 4 ? 2 : 1, 5);
   dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
   kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc, c->org[0], c->org[1],
                                           c->org[2]);
@@ -1938,9 +1987,11 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   const int v = (int)value;
   if (k == "variant") c->variant = v;
   else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
-  else if (k == "zchunk") { if (v < 2) INS_FAIL(c, "zchunk must be >= 2"); c->zchunk = v; }
+  else if (k == "zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "zchunk must be 0 (automatic) or >= 2"); c->zchunk = v; }
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
+  else if (k == "rows2d") c->rows2d = v != 0;
+  else if (k == "stage_x2") { if (v < 0 || v > 2) INS_FAIL(c, "stage_x2 must be 0, 1 or 2"); c->stage_x2 = v; }
   else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
   else if (k == "fft_pipe") {
     if (c->plans) INS_FAIL(c, "fft_pipe must be set before the first pressure solve");
@@ -1953,7 +2004,7 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
     c->fft_chunk = v;
   }
   else if (k == "smag_ty") { if (v != 8 && v != 16) INS_FAIL(c, "smag_ty must be 8 or 16"); c->smag_ty = v; }
-  else if (k == "smag_zchunk") { if (v < 2) INS_FAIL(c, "smag_zchunk must be >= 2"); c->smag_zchunk = v; }
+  else if (k == "smag_zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "smag_zchunk must be 0 (automatic) or >= 2"); c->smag_zchunk = v; }
   else if (k == "p2p_halo") c->p2p_halo = v != 0;
   else if (k == "p2p_fused") { if (v < 0 || v > 2) INS_FAIL(c, "p2p_fused must be 0, 1 or 2"); c->p2p_fused = v; }
   else if (k == "p2p") {

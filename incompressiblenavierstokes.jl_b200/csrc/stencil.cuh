@@ -398,6 +398,81 @@ __global__ void k_gradient_z(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// 2-D forms marching RPT rows per thread (the one-cell-per-thread kernels reach about half of the HBM bandwidth
+// in 2-D: too few bytes in flight per thread, 4096^2 measured).  All loads of a thread's rows are issued before its
+// first store; values shared by consecutive rows (p(j+1), u_y(j-1)) are loaded once.  Same arithmetic, same order.
+// Measured at 4096^2 Float32: divergence 0.072 -> 0.041 ms, gradient 0.103 -> 0.059 ms.  (The same treatment of the
+// stage kernel, two rows per thread, was slower -- 0.199 -> 0.235 ms -- and is not kept.)
+// ---------------------------------------------------------------------------------------------
+template <typename T, int MODE, int RPT>
+__global__ void k_gradient_y(View<T> out, View<const T> p, Geo gp, Rh<T> rh) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j0 = (blockIdx.y * blockDim.y + threadIdx.y) * RPT;
+  if (i >= gp.n[0] || j0 >= gp.n[1]) return;
+  int ip = i + 1;
+  if (gp.wrap[0] && ip >= gp.n[0]) ip -= gp.n[0];
+  const int nr = min(RPT, gp.n[1] - j0);
+  T pc[RPT + 1], px[RPT];
+#pragma unroll
+  for (int m = 0; m <= RPT; m++) {
+    int jj = j0 + m;
+    if (gp.wrap[1] && jj >= gp.n[1]) jj -= gp.n[1];
+    if (m <= nr) pc[m] = __ldg(p.p + (i64)jj * p.sy + i);
+    if (m < nr) px[m] = __ldg(p.p + (i64)jj * p.sy + ip);
+  }
+  T *o = out.p + (i64)j0 * out.sy + i;
+  if (MODE == 0) {
+#pragma unroll
+    for (int m = 0; m < RPT; m++)
+      if (m < nr) {
+        o[m * out.sy] = (px[m] - pc[m]) * rh.v[0];
+        o[m * out.sy + out.sc] = (pc[m + 1] - pc[m]) * rh.v[1];
+      }
+  } else {
+    T u[RPT][2];
+#pragma unroll
+    for (int m = 0; m < RPT; m++)
+      if (m < nr) { u[m][0] = o[m * out.sy]; u[m][1] = o[m * out.sy + out.sc]; }
+#pragma unroll
+    for (int m = 0; m < RPT; m++)
+      if (m < nr) {
+        o[m * out.sy] = u[m][0] - (px[m] - pc[m]) * rh.v[0];
+        o[m * out.sy + out.sc] = u[m][1] - (pc[m + 1] - pc[m]) * rh.v[1];
+      }
+  }
+}
+
+template <typename T, int RPT>
+__global__ void k_divergence_y(View<T> out, View<const T> u, Geo g, Rh<T> rh, T vol, int scale) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int j0 = (blockIdx.y * blockDim.y + threadIdx.y) * RPT;
+  if (i >= g.n[0] || j0 >= g.n[1]) return;
+  int im = i - 1;
+  if (g.wrap[0] && im < 0) im += g.n[0];
+  const int nr = min(RPT, g.n[1] - j0);
+  T ux[RPT], uxm[RPT], uy[RPT + 1];  // uy[m] = u_y(i, j0 + m - 1)
+#pragma unroll
+  for (int m = 0; m <= RPT; m++) {
+    int jj = j0 + m - 1;
+    if (g.wrap[1] && jj < 0) jj += g.n[1];
+    if (m <= nr) uy[m] = __ldg(u.p + u.sc + (i64)jj * u.sy + i);
+    if (m >= 1 && m <= nr) {
+      ux[m - 1] = __ldg(u.p + (i64)jj * u.sy + i);
+      uxm[m - 1] = __ldg(u.p + (i64)jj * u.sy + im);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < RPT; m++)
+    if (m < nr) {
+      T d = T(0);
+      d += (ux[m] - uxm[m]) * rh.v[0];
+      d += (uy[m + 1] - uy[m]) * rh.v[1];
+      if (scale) d = d * vol;
+      out.p[(i64)(j0 + m) * out.sy + i] = d;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
 // observers (processors.jl:77-198): fields derived from u, on the reference layout (raw base pointer,
 // N = n+2 points per axis incl. ghosts; the ghosts of u must be valid).
 // ---------------------------------------------------------------------------------------------

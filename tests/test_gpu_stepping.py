@@ -223,10 +223,16 @@ def test_kernel_variants_bit_identical(T, smag):
                          ("tiled16", dict(variant=1, tile_y=16, zchunk=64, fuse_gradient=1)),
                          ("tiled8_zc16", dict(variant=1, tile_y=8, zchunk=16, fuse_gradient=1)),
                          ("tiled16_zc7_nofuse", dict(variant=1, tile_y=16, zchunk=7, fuse_gradient=0)),
-                         ("tma_zc64", dict(variant=2, zchunk=64)),
+                         ("tma_zc64", dict(variant=2, zchunk=64, stage_x2=0)),
                          ("tma_zc7", dict(variant=2, zchunk=7)),
                          ("tma_zc2", dict(variant=2, zchunk=2)),
-                         ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1)),
+                         # two cells per thread on packed FP32 (Float32 only; exact = scalar multiplies, packed adds)
+                         ("tma_x2_zc64", dict(variant=2, zchunk=64, stage_x2=1)),
+                         ("tma_x2_zc7", dict(variant=2, zchunk=7)),
+                         ("tma_x2_zc2", dict(variant=2, zchunk=2)),
+                         ("tma_x2fused_zc64", dict(variant=2, zchunk=64, stage_x2=2)),
+                         ("tma_x2fused_zc5", dict(variant=2, zchunk=5)),
+                         ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1, stage_x2=1)),
                          ("tma_smag_v2_zc128", dict(variant=2, smag_v=2, smag_zchunk=128)),
                          ("tma_smag_v2_zc7", dict(variant=2, smag_v=2, smag_zchunk=7)),
                          ("tma_smag_v2_zc2", dict(variant=2, smag_v=2, smag_zchunk=2)),
@@ -238,8 +244,39 @@ def test_kernel_variants_bit_identical(T, smag):
         results[name] = (ins.to_host(u), ke)
     ref_u, ref_ke = results["naive"]
     for name, (u, ke) in results.items():
+        if "fused" in name and T == np.float32:
+            # FFMA2-contracted products (f32x2.cuh): same operations with fewer roundings, not bit-identical
+            compare(name, u, ref_u, 2e-6)
+            assert np.allclose(ke, ref_ke, rtol=1e-6, atol=0), name
+            continue
         compare(name, u, ref_u, 0, exact=True)
         assert np.array_equal(ke, ref_ke), name
+
+
+@pytest.mark.parametrize("T", [np.float64, np.float32], ids=["f64", "f32"])
+@pytest.mark.parametrize("n,smag", [((64, 48), False), ((70, 38), True), ((32, 6), False)], ids=["64x48", "70x38_smag", "32x6"])
+def test_2d_row_marching_kernels_bit_identical(T, n, smag):
+    """2-D: the kernels that march several rows per thread (divergence, gradient) perform the arithmetic of
+    the one-cell-per-thread kernels: bit-identical u, p and energies, also when the row count is not a multiple of
+    the rows per thread."""
+    import insb200 as ins
+    from insb200.api import _rk_steps
+
+    so, sc = make_pair(n, T, force=True, smag=smag)
+    theta = 0.17 if smag else None
+    u0 = o.random_field(so, kp=4, rng=np.random.default_rng(5))
+    m = ins.RKMethods.RK44(T=T)
+    res = {}
+    for rows in (0, 1):
+        set_param(sc, "rows2d", rows)
+        u = ins.to_device(u0, sc)
+        _, ke = _rk_steps(m, sc, u, 0.0, 1e-3, 3, theta, ke_hist=True)
+        p = ins.pressure(u, None, 0.0, sc)
+        G = ins.pressuregradient(p, sc)
+        d = ins.divergence(ins.apply_bc_u(G, 0.0, sc), sc)
+        res[rows] = [ins.to_host(x) for x in (u, p, G, d)] + [ke]
+    for a, b, name in zip(res[1], res[0], ("u", "p", "grad p", "div grad p", "ke")):
+        compare(name, a, b, 0, exact=True)
 
 
 def test_checkpoint_restart_is_bit_identical(tmp_path):
