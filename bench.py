@@ -237,7 +237,7 @@ def cpu_sample(wl, steps=1, n=None):
 
 # words (sizeof(T)) per cell per LAUNCH of each library kernel: the algorithmic minimum, every
 # logical field read / written once (DESIGN.md "Kernels and rooflines")
-def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False):
+def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False, fused2d=False):
     """Algorithmic words per cell per LAUNCH of each library kernel (every logical field read / written once)."""
     ntens = D * (D + 1) // 2
     extra = (D if force else 0)
@@ -263,6 +263,10 @@ def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False):
         w["momentum_stage_last"] = 3.0 * D + 2 + D * (nstages - 1) + extra + sadd
         # R u, R p (all but the first stage), W s; sigma never leaves shared memory
         w["smagorinsky_fused"] = 2.0 * D + (nstages - 1.0) / nstages
+    if fused2d:
+        # 2-D fused warp-marching stage kernel (stage2d.cuh): as the TMA kernels, one timer for all stages
+        first, mid, last = 3.0 * D + 1, 4.0 * D + 2, 3.0 * D + 2 + D * (nstages - 1)
+        w["momentum_stage"] = (first + (nstages - 2) * mid + last) / nstages + extra
     if zsolve:
         # k_zsolve does the last-axis transforms and the symbol in one read + write of the half spectrum
         # ("poisson_scale" timer); cuFFT only transforms the D-1 in-plane axes
@@ -418,7 +422,8 @@ def run_ours(args, wl):
     cells_local = cells / world
     nz_glob = n[-1]
     words = kernel_words(D, theta is not None, wl["force"], tma=(D == 3 and base_n % 32 == 0),
-                         zsolve=(D == 3 and 8 <= nz_glob <= 2048 and nz_glob & (nz_glob - 1) == 0))
+                         zsolve=(D == 3 and 8 <= nz_glob <= 2048 and nz_glob & (nz_glob - 1) == 0),
+                         fused2d=(D == 2 and world == 1 and theta is None and "divergence" not in timers))
     peak, peak_src = peaks()
     kern = {}
     for name, (tms, cnt) in timers.items():

@@ -14,7 +14,7 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libinsb200.so")
 SOURCES = [os.path.join(CSRC, "insb200.cu"), os.path.join(CSRC, "temperature.cu")]
 OBJDIR = os.path.join(HERE, "build")  # git-ignored object cache: only stale translation units are recompiled
-HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "zsolve.cuh")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "stage2d.cuh", "zsolve.cuh")] + [
     os.path.join(os.path.dirname(HERE), "include", "insb200.h")
 ]
 

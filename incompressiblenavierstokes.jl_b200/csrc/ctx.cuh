@@ -95,6 +95,8 @@ struct insb200_ctx {
   int smag_zchunk = 0;     // planes marched per block of k_smag3d_v2 (0 = automatic, auto_zchunk)
   int zchunk = 0;          // stage kernels: planes marched per block (0 = automatic for the TMA kernels, 64 for the LDG-tiled ones)
   int nsm = 148;           // SMs of the device
+  int fuse2d = 1;          // 2-D, one rank: fused warp-marching stage kernel (stage2d.cuh); 0 = stage + divergence + gradient kernels
+  int rows_chunk = 0;      // rows marched per block of k_stage2d_warp (0 = automatic)
   int rows2d = 1;          // 2-D: divergence / gradient kernels march several rows per thread (0 = one cell per thread)
   int padded = 0;          // 1: padded layout with real ghost cells (3-D)
   int org[3] = {0, 0, 0};  // interior origin inside the padded box (elements)

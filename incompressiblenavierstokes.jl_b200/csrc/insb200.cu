@@ -12,6 +12,7 @@
 #include "tiled.cuh"
 #include "tma_stage.cuh"
 #include "tma_stage_x2.cuh"
+#include "stage2d.cuh"
 #include "zsolve.cuh"
 
 namespace insb200 {
@@ -1722,6 +1723,29 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
   return 0;
 }
 
+// fused 2-D stage kernel (stage2d.cuh): one rank, periodic by index wrap, rows of at least 3 cells
+template <typename T, int D>
+static bool fused2d_supported(const insb200_ctx *c) {
+  return D == 2 && c->nranks == 1 && c->fuse2d && c->nloc[0] >= 4 && c->nloc[1] >= 4;
+}
+template <typename T>
+static int launch_stage2d(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh) {
+  const int bx = ((c->nloc[0] + kS2Cols - 1) / kS2Cols + kS2Warps - 1) / kS2Warps;
+  // rows per block: the march is a serial chain per warp, so many short chunks beat few long ones (4096^2 F32:
+  // 0.434 / 0.266 / 0.251 / 0.231 / 0.225 ms at 512 / 256 / 128 / 64 / 32 rows); the pre-iteration costs one row per chunk
+  int rc = c->rows_chunk;
+  if (rc <= 0) {
+    const int chunks = std::max((c->nsm * 16) / bx, (c->nloc[1] + 31) / 32);
+    rc = std::min(32, std::max(8, (c->nloc[1] + chunks - 1) / chunks));
+  }
+  rc = std::min(rc, c->nloc[1]);
+  dim3 grd(bx, (c->nloc[1] + rc - 1) / rc, 1);
+  if (a.pin) k_stage2d_warp<T, true><<<grd, 32 * kS2Warps, 0, c->stream>>>(a, g, visc, rh, volume<T>(c), rc);
+  else k_stage2d_warp<T, false><<<grd, 32 * kS2Warps, 0, c->stream>>>(a, g, visc, rh, volume<T>(c), rc);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
 // one timestep!: state in ubuf[0] (compact), result in ubuf[0] (buffers rotated).
 //
 // Tiled path (3-D, tile-aligned n): per stage ONE kernel produces k_i, u' and the Poisson right-hand
@@ -1734,8 +1758,9 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
   const Geo g = geo_compact(c);
   const T visc = T(1) / T(c->Re);
   const Rh<T> rh = make_rh<T>(c);
-  const bool tiled = tiled_stage_supported<T, D>(c);
-  const bool fuse_grad = tiled && c->fuse_gradient;
+  const bool f2d = !smag && fused2d_supported<T, D>(c);
+  const bool tiled = f2d || tiled_stage_supported<T, D>(c);
+  const bool fuse_grad = f2d || (tiled && c->fuse_gradient);
   const i64 goff = c->corg;
   T *pr = (T *)c->preal + goff;
   int cur = 0;
@@ -1776,11 +1801,12 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
       }
       {
         ScopedTimer tm(c, TM_STAGE);
-        INS_TRY((launch_stage_tiled<T, D>(c, a, g, visc, rh, smag)));
+        if constexpr (D == 2) INS_TRY((launch_stage2d<T>(c, a, g, visc, rh)));  // f2d (tiled implies it in 2-D)
+        else INS_TRY((launch_stage_tiled<T, D>(c, a, g, visc, rh, smag)));
       }
       // u' halos: the minus side for the chunk-first planes of the divergence, both for the next stage
       INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, 1, 1)));
-      INS_TRY((launch_divergence_planes<T>(c, pr, (const T *)c->ubuf[nxt] + goff, g)));
+      if constexpr (D == 3) INS_TRY((launch_divergence_planes<T>(c, pr, (const T *)c->ubuf[nxt] + goff, g)));
       INS_TRY((poisson_solve<T, D>(c)));
       const bool last = i == tb.s - 1;
       if (fuse_grad && !last) {
@@ -1991,6 +2017,8 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;
   else if (k == "zsolve") c->zsolve = v != 0;
   else if (k == "rows2d") c->rows2d = v != 0;
+  else if (k == "fuse2d") c->fuse2d = v != 0;
+  else if (k == "rows_chunk") { if (v != 0 && v < 2) INS_FAIL(c, "rows_chunk must be 0 (automatic) or >= 2"); c->rows_chunk = v; }
   else if (k == "stage_x2") { if (v < 0 || v > 2) INS_FAIL(c, "stage_x2 must be 0, 1 or 2"); c->stage_x2 = v; }
   else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
   else if (k == "fft_pipe") {

@@ -254,7 +254,8 @@ def test_kernel_variants_bit_identical(T, smag):
 
 
 @pytest.mark.parametrize("T", [np.float64, np.float32], ids=["f64", "f32"])
-@pytest.mark.parametrize("n,smag", [((64, 48), False), ((70, 38), True), ((32, 6), False)], ids=["64x48", "70x38_smag", "32x6"])
+@pytest.mark.parametrize("n,smag", [((64, 48), False), ((70, 38), True), ((32, 6), False), ((58, 30), False), ((128, 64), False)],
+                         ids=["64x48", "70x38_smag", "32x6", "58x30", "128x64"])
 def test_2d_row_marching_kernels_bit_identical(T, n, smag):
     """2-D: the kernels that march several rows per thread (divergence, gradient) perform the arithmetic of
     the one-cell-per-thread kernels: bit-identical u, p and energies, also when the row count is not a multiple of
@@ -267,16 +268,22 @@ def test_2d_row_marching_kernels_bit_identical(T, n, smag):
     u0 = o.random_field(so, kp=4, rng=np.random.default_rng(5))
     m = ins.RKMethods.RK44(T=T)
     res = {}
-    for rows in (0, 1):
-        set_param(sc, "rows2d", rows)
+    # (rows2d, fuse2d, rows_chunk): unfused one-cell kernels = reference; row-marching divergence / gradient; the fused
+    # warp-marching stage kernel (stage2d.cuh; falls back to the unfused path with a closure model) with automatic,
+    # tiny and odd row chunks
+    configs = [(0, 0, 0), (1, 0, 0), (1, 1, 0), (0, 1, 5), (1, 1, 2), (1, 1, 17)]
+    for cfg in configs:
+        for k, v in zip(("rows2d", "fuse2d", "rows_chunk"), cfg):
+            set_param(sc, k, v)
         u = ins.to_device(u0, sc)
         _, ke = _rk_steps(m, sc, u, 0.0, 1e-3, 3, theta, ke_hist=True)
         p = ins.pressure(u, None, 0.0, sc)
         G = ins.pressuregradient(p, sc)
         d = ins.divergence(ins.apply_bc_u(G, 0.0, sc), sc)
-        res[rows] = [ins.to_host(x) for x in (u, p, G, d)] + [ke]
-    for a, b, name in zip(res[1], res[0], ("u", "p", "grad p", "div grad p", "ke")):
-        compare(name, a, b, 0, exact=True)
+        res[cfg] = [ins.to_host(x) for x in (u, p, G, d)] + [ke]
+    for cfg in configs[1:]:
+        for a, b, name in zip(res[cfg], res[configs[0]], ("u", "p", "grad p", "div grad p", "ke")):
+            compare(f"{name} {cfg}", a, b, 0, exact=True)
 
 
 def test_checkpoint_restart_is_bit_identical(tmp_path):
