@@ -345,6 +345,9 @@ def run_ours(args, wl):
     if world > 1:
         import torch.distributed as dist
     torch.cuda.set_device(backend.device)
+    # a non-default stream: the library replays whole steps as CUDA graphs on small grids, and capture is not
+    # allowed on the legacy default stream (Julia's CUDA.jl runs on a task-local stream as well)
+    torch.cuda.set_stream(torch.cuda.Stream(device=backend.device))
     D = wl["D"]
     T = np.float32 if wl["T"] == "float32" else np.float64
     base_n = args.n or wl["n"]
@@ -387,7 +390,7 @@ def run_ours(args, wl):
     if sampler:
         sampler.start()
         time.sleep(0.3)
-    l0, f0 = lib.insb200_launch_count(h), lib.insb200_fft_exec_count(h)
+    l0, f0, g0 = lib.insb200_launch_count(h), lib.insb200_fft_exec_count(h), lib.insb200_graph_replays(h)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     w0 = time.perf_counter()
@@ -400,6 +403,7 @@ def run_ours(args, wl):
     w1 = time.perf_counter()
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches, ffts = lib.insb200_launch_count(h) - l0, lib.insb200_fft_exec_count(h) - f0
+    graph_replays = lib.insb200_graph_replays(h) - g0
     clocks = sampler.stop(w0, w1) if sampler else None
     ms_step = ms / K
     value = cells / (ms_step * 1e-3) / 1e6
@@ -483,6 +487,7 @@ def run_ours(args, wl):
                    "l2": "inputs larger than L2 (state >> 126 MB), no flush",
                    "init": "24 random Fourier modes, Orlandi-type amplitudes, projected on the device"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "cufft_execs": int(ffts),
+        "graph_replays": int(graph_replays),
         "roofline": roofline,
         "step_roofline": {"model_bytes_per_cell_step": model_bytes, "achieved": step_gbs, "peak": peak, "unit": "GB/s",
                           "frac": step_gbs / peak, "note": "SURVEY 8d model (46D+8 words, closure fused) per GPU"},

@@ -218,6 +218,10 @@ int insb200_set_variant(insb200_ctx *ctx, int variant);
  *   loader of stage i+1 instead of a gradient kernel). */
 int insb200_set_param(insb200_ctx *ctx, const char *name, double value);
 
+/* Whole RK steps are replayed as CUDA graphs where that is possible (one rank, fixed dt, a non-default stream, timers
+ * off; set_param("graphs", 0) disables it): number of steps that ran as a graph replay so far. */
+long long insb200_graph_replays(const insb200_ctx *ctx);
+
 /* Device memory owned by the ctx, in bytes. */
 long long insb200_workspace_bytes(const insb200_ctx *ctx);
 

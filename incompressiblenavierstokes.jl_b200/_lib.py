@@ -56,6 +56,7 @@ PROTOTYPES = {
     "insb200_interpolate_w_p": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_velocitynorm": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_workspace_bytes": (c_ll, [c_void_p]),
+    "insb200_graph_replays": (c_ll, [c_void_p]),
     "insb200_set_temperature": (c_int, [c_void_p, c_double, c_double, c_double, c_double, c_double, c_int, c_int]),
     "insb200_apply_bc_temp": (c_int, [c_void_p, c_void_p]),
     "insb200_convection_diffusion_temp": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),

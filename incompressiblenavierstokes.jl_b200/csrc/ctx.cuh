@@ -158,6 +158,20 @@ struct insb200_ctx {
   void *tws = nullptr;
   size_t tws_bytes = 0;
 
+  // CUDA graphs of whole RK steps (insb200.cu: rk_step_graphed): one instantiated graph per buffer permutation
+  struct StepGraph {
+    std::vector<unsigned long long> key;   // buffers, stream, dt, theta, tableau
+    cudaGraphExec_t exec = nullptr;
+    void *post[5] = {nullptr};             // ubuf[0..2], preal, preal2 after the step (the step rotates its buffers)
+    long long launches = 0, fft_execs = 0; // per replay
+  };
+  std::vector<StepGraph> graphs;
+  std::vector<std::vector<unsigned long long>> graph_seen;
+  bool graph_warm = false;                              // one eager step has run since the last (re)configuration
+  int use_graphs = -1;                                  // param "graphs": 1 on, 0 off, -1 automatic (slabs of <= 2^22 cells)
+  long long graph_replays = 0;
+  int graph_misses = 0;                                 // captures since the last replay
+
   // FFT plans
   cufftHandle plan_fwd = 0, plan_inv = 0;               // nranks==1: D-dim R2C / C2R
   cufftHandle plan_fwd_in = 0, plan_inv_in = 0;         // nranks>1: in-slab transforms

@@ -17,6 +17,7 @@
 
 namespace insb200 {
 thread_local std::string g_create_error;
+static void clear_graphs(insb200_ctx *c);  // CUDA graphs of whole RK steps (below, next to the stepping loops)
 
 static const int kG = 2;  // ghost planes on the decomposed axis of compact buffers (nranks > 1)
 
@@ -277,6 +278,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   if (!c) return 0;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  clear_graphs(c);
   if (c->plans) {
     if (c->plan_fwd) cufftDestroy(c->plan_fwd);
     if (c->plan_inv) cufftDestroy(c->plan_inv);
@@ -321,6 +323,7 @@ extern "C" const char *insb200_last_error(const insb200_ctx *c) {
 
 extern "C" int insb200_set_stream(insb200_ctx *c, void *s) {
   CHECK_CTX(c);
+  if (c->stream != (cudaStream_t)s) clear_graphs(c);
   c->stream = (cudaStream_t)s;  // NULL = the CUDA legacy default stream (not the ctx-owned one)
   if (c->plans) {
     cufftHandle hs[] = {c->plan_fwd, c->plan_inv, c->plan_fwd_in, c->plan_inv_in, c->plan_last};
@@ -1291,6 +1294,7 @@ extern "C" int insb200_apply_bc_p(insb200_ctx *c, void *p) {
 }
 extern "C" int insb200_set_bodyforce(insb200_ctx *c, const void *f) {
   API_PROLOG(c);
+  clear_graphs(c);
   if (!f) {
     if (c->force) {
       INS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1832,6 +1836,85 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
   return 0;
 }
 
+// ---- CUDA graphs --------------------------------------------------------------------------------------------------
+// A step is a fixed sequence of 20-40 launches (own kernels + cuFFT) on one stream; on small grids (128^3, 256^2) the
+// launch overhead is a large part of it.  With a fixed dt the sequence repeats with the buffers rotated (period 2-4).
+// The first step after any (re)configuration runs eagerly -- lazy allocations, function attributes and tensor-map
+// descriptors happen there --; from then on every new (buffers, dt, theta, tableau) state is captured once and
+// replayed afterwards.  One rank only (NCCL and the second stream of the pipelined transposes stay outside), not on
+// the legacy default stream (capture is not allowed there), not while the per-kernel timers record, and by default
+// only for slabs of up to 2^22 cells (above that a step takes milliseconds and the capture would not pay).
+static void clear_graphs(insb200_ctx *c) {
+  for (auto &e : c->graphs) if (e.exec) cudaGraphExecDestroy(e.exec);
+  c->graphs.clear();
+  c->graph_seen.clear();
+  c->graph_warm = false;
+  c->graph_misses = 0;
+}
+
+template <typename T, int D>
+static int rk_step_graphed(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
+  const bool wanted = c->use_graphs > 0 || (c->use_graphs < 0 && c->cint <= ((i64)1 << 22));
+  const bool usable = wanted && c->nranks == 1 && !c->profiling && c->stream != nullptr && c->stream != cudaStreamLegacy &&
+                      c->stream != cudaStreamPerThread;
+  if (!usable) return rk_step_compact<T, D>(c, tb, dt, theta);
+  if (!c->graph_warm) {
+    c->graph_warm = true;
+    return rk_step_compact<T, D>(c, tb, dt, theta);
+  }
+  std::vector<unsigned long long> key;
+  auto push_ptr = [&](const void *p) { key.push_back((unsigned long long)(uintptr_t)p); };
+  auto push_f64 = [&](double v) { unsigned long long b; memcpy(&b, &v, sizeof b); key.push_back(b); };
+  for (void *p : c->ubuf) push_ptr(p);
+  push_ptr(c->preal); push_ptr(c->preal2); push_ptr((const void *)c->stream);
+  push_f64(dt); push_f64(theta);
+  key.push_back((unsigned long long)tb.s);
+  for (int i = 0; i < tb.s * tb.s; i++) push_f64(tb.A[i]);
+  for (auto &e : c->graphs)
+    if (e.key == key) {
+      INS_CUDA(c, cudaGraphLaunch(e.exec, c->stream));
+      for (int b = 0; b < 3; b++) c->ubuf[b] = e.post[b];
+      c->preal = e.post[3]; c->preal2 = e.post[4];
+      c->launches += e.launches; c->fft_execs += e.fft_execs;
+      c->graph_replays++;
+      c->graph_misses = 0;
+      return 0;
+    }
+  // adaptive dt: the keys never repeat -- after 8 captures in a row without a replay stop capturing
+  if (c->graph_misses >= 8) return rk_step_compact<T, D>(c, tb, dt, theta);
+  c->graph_misses++;
+  if (c->graphs.size() >= 32) { clear_graphs(c); c->graph_warm = true; }
+  // new state: capture.  The step mutates the buffer rotation on the host; keep the state to fall back
+  void *pre[5] = {c->ubuf[0], c->ubuf[1], c->ubuf[2], c->preal, c->preal2};
+  const long long l0 = c->launches, f0 = c->fft_execs;
+  cudaGraph_t graph = nullptr;
+  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    c->use_graphs = 0;
+    return rk_step_compact<T, D>(c, tb, dt, theta);
+  }
+  const int r = rk_step_compact<T, D>(c, tb, dt, theta);
+  const cudaError_t ce = cudaStreamEndCapture(c->stream, &graph);
+  insb200_ctx::StepGraph e;
+  if (r == 0 && ce == cudaSuccess && graph && cudaGraphInstantiate(&e.exec, graph, 0) == cudaSuccess) {
+    cudaGraphDestroy(graph);
+    e.key = key;
+    e.post[0] = c->ubuf[0]; e.post[1] = c->ubuf[1]; e.post[2] = c->ubuf[2]; e.post[3] = c->preal; e.post[4] = c->preal2;
+    e.launches = c->launches - l0; e.fft_execs = c->fft_execs - f0;
+    INS_CUDA(c, cudaGraphLaunch(e.exec, c->stream));
+    c->graphs.push_back(e);
+    return 0;
+  }
+  // capture failed: nothing ran; restore the rotation, stop using graphs on this ctx and run the step eagerly
+  if (graph) cudaGraphDestroy(graph);
+  cudaGetLastError();
+  for (int b = 0; b < 3; b++) c->ubuf[b] = pre[b];
+  c->preal = pre[3]; c->preal2 = pre[4];
+  c->launches = l0; c->fft_execs = f0;
+  c->use_graphs = 0;
+  return rk_step_compact<T, D>(c, tb, dt, theta);
+}
+
 template <typename T, int D>
 static int reduce_compact(insb200_ctx *c, double *out4) {
   INS_TRY((halo_compact<T>(c, c->ubuf[0], D, 1, 0)));
@@ -1854,7 +1937,7 @@ static int op_rk_steps(insb200_ctx *c, void *u, double *t, double dt, int nsteps
   if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[0] = o[0]; }
   T tt = T(*t);
   for (int n = 0; n < nsteps; n++) {
-    INS_TRY((rk_step_compact<T, D>(c, tb, dt, theta)));
+    INS_TRY((rk_step_graphed<T, D>(c, tb, dt, theta)));
     tt = tt + T(tb.c[tb.s - 1]) * T(dt);  // t = tstart + c[i]*dt (:32)
     if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[n + 1] = o[0]; }
   }
@@ -1887,7 +1970,7 @@ static int op_solve_host(insb200_ctx *c, void *u_host, double t0, double tend, d
     const T d = (te - t) / T((double)nstep);
     if (max_steps > 0 && nstep > max_steps) nstep = max_steps;
     for (; n < nstep; n++) {
-      INS_TRY((rk_step_compact<T, D>(c, tb, (double)d, theta)));
+      INS_TRY((rk_step_graphed<T, D>(c, tb, (double)d, theta)));
       t = t + T(tb.c[tb.s - 1]) * d;
       if (ke_hist && nk < ke_cap) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[nk++] = o[0]; }
     }
@@ -1965,6 +2048,7 @@ extern "C" double insb200_model_bytes_per_cell_step(const insb200_ctx *c, int ns
 extern "C" long long insb200_launch_count(const insb200_ctx *c) { return c ? c->launches : 0; }
 extern "C" long long insb200_fft_exec_count(const insb200_ctx *c) { return c ? c->fft_execs : 0; }
 extern "C" long long insb200_workspace_bytes(const insb200_ctx *c) { return c ? c->ws_bytes : 0; }
+extern "C" long long insb200_graph_replays(const insb200_ctx *c) { return c ? c->graph_replays : 0; }
 
 static int drain_timers(insb200_ctx *c) {
   INS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -2003,6 +2087,7 @@ extern "C" int insb200_timers(insb200_ctx *c, const char **names, double *ms, lo
 }
 extern "C" int insb200_set_variant(insb200_ctx *c, int variant) {
   if (!c) return 1;
+  clear_graphs(c);
   c->variant = variant;
   return 0;
 }
@@ -2011,7 +2096,9 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   if (!name) INS_FAIL(c, "parameter name is NULL");
   const std::string k(name);
   const int v = (int)value;
+  clear_graphs(c);  // a captured step holds the launch configuration of the parameters it was captured with
   if (k == "variant") c->variant = v;
+  else if (k == "graphs") c->use_graphs = v;  // 1 on, 0 off, -1 automatic (small grids)
   else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
   else if (k == "zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "zchunk must be 0 (automatic) or >= 2"); c->zchunk = v; }
   else if (k == "fuse_gradient") c->fuse_gradient = v != 0;

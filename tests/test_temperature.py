@@ -47,6 +47,21 @@ def test_oracle_temperature_coefficients():
         assert np.isclose(q3.alpha1, q3.alpha3) and np.isclose(q3.gamma, 1)
 
 
+def test_mirror_temperature_equation_matches_oracle():
+    """The host mirror forms the coefficients of setup.jl:56-86 exactly like the oracle (pure host code)."""
+    import insb200 as ins
+
+    for T in (np.float32, np.float64):
+        for nd in (1, 2, 3):
+            a = ins.temperature_equation(T(0.71), T(1e6), T(0.1), nondim_type=nd, gdir=1, dodissipation=False)
+            b = o.temperature_equation(T(0.71), T(1e6), T(0.1), nondim_type=nd, gdir=1, dodissipation=False)
+            for k in ("alpha1", "alpha2", "alpha3", "alpha4", "gamma"):
+                assert getattr(a, k) == getattr(b, k) and getattr(a, k).dtype == T, (k, nd)
+            assert (a.gdir, a.dodissipation) == (b.gdir, b.dodissipation)
+    with pytest.raises(ValueError):
+        ins.temperature_equation(1.0, 1.0, 1.0, nondim_type=4)
+
+
 @pytest.mark.parametrize("n", [(16, 24), (8, 12, 16)], ids=["2d", "3d"])
 def test_oracle_temperature_transport_identities(n):
     so = osetup(n)
