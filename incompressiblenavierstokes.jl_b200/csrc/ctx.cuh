@@ -166,7 +166,6 @@ struct insb200_ctx {
     long long launches = 0, fft_execs = 0; // per replay
   };
   std::vector<StepGraph> graphs;
-  std::vector<std::vector<unsigned long long>> graph_seen;
   bool graph_warm = false;                              // one eager step has run since the last (re)configuration
   int use_graphs = -1;                                  // param "graphs": 1 on, 0 off, -1 automatic (slabs of <= 2^22 cells)
   long long graph_replays = 0;

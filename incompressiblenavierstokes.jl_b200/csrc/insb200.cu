@@ -1847,7 +1847,6 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
 static void clear_graphs(insb200_ctx *c) {
   for (auto &e : c->graphs) if (e.exec) cudaGraphExecDestroy(e.exec);
   c->graphs.clear();
-  c->graph_seen.clear();
   c->graph_warm = false;
   c->graph_misses = 0;
 }
