@@ -1462,9 +1462,11 @@ static const int kTX = 32, kTY = 16;
 
 template <typename T, int D>
 static bool tma_supported(const insb200_ctx *c) {
-  // 32-bit element offsets inside the kernels: the three components of one buffer must stay below 2^31
+  // the closure kernels address the three components of one buffer with UNSIGNED 32-bit element offsets
+  // (tma_stage.cuh; the stage kernel uses 64-bit byte offsets per component): a padded vector field must stay
+  // below 2^32 elements -- 1024^3 on one GPU qualifies (3.35e9); larger slabs take the LDG-tiled kernels
   return D == 3 && c->padded && c->variant >= 2 && c->nloc[0] % kTX == 0 && c->nloc[1] % kTY == 0 && c->nloc[2] >= 2 &&
-         3 * c->ccomp < ((i64)1 << 31);
+         3 * c->ccomp < ((i64)1 << 32);
 }
 
 static const int kNS = 5;  // velocity plane slots of the stage kernel (prefetch distance 2 planes)
