@@ -103,6 +103,7 @@ struct insb200_ctx {
   int ext[3] = {1, 1, 1};  // padded extents PX, PY, PZ
   int gm = 0, gp = 0;      // ghost layers kept valid on the minus / plus side (y, z; x has more room)
   int fuse_gradient = 1;   // apply the projection of stage i in the loader of stage i+1
+  int zradix16 = 1;        // k_zsolve, Float32: radix-16 passes where they save a trip through shared memory
   int zcols = 0, zthreads = 256;  // k_zsolve tuning: columns per tile (0 = largest that fits 64 KB), threads per block
   int zsolve = 1;          // 3-D: own fused last-axis transform + symbol kernel instead of cuFFT's z passes
   cudaStream_t stream = nullptr;

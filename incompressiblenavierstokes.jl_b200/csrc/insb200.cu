@@ -729,6 +729,14 @@ static int zsolve_prepare(insb200_ctx *c, ZRadix &rad) {
   rad.n = 0;
   int m = 0;
   while ((1 << m) < nz) m++;
+  if (sizeof(T) == 4 && c->zradix16) {
+    // fewest trips through shared memory with radices up to 16 (Float32: 16 complex values in registers):
+    // ceil(m / 4) digits as even as possible, the larger ones last -- 1024 = 8 * 8 * 16 (5 passes instead of the 7 of
+    // 8 * 8 * 8 * 2), 256 = 16 * 16, 512 = 8 * 8 * 8 as before
+    const int nd = (m + 3) / 4, base = m / nd, rem = m % nd;
+    for (int i = 0; i < nd; i++) rad.r[rad.n++] = base + (i >= nd - rem ? 1 : 0);
+    return 0;
+  }
   while (m >= 3) { rad.r[rad.n++] = 3; m -= 3; }  // log2 of the radix: 8, 8, .. then 4 or 2
   if (m > 0) rad.r[rad.n++] = m;
   return 0;
@@ -2128,6 +2136,7 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
     c->p2p_enable = v != 0;
   }
   else if (k == "zcols") { if (v != 0 && v != 4 && v != 8 && v != 16) INS_FAIL(c, "zcols must be 0, 4, 8 or 16"); c->zcols = v; }
+  else if (k == "zradix16") c->zradix16 = v != 0;
   else if (k == "zthreads") { if (v < 64 || v > 512 || v % 32) INS_FAIL(c, "zthreads must be a multiple of 32 in [64, 512]"); c->zthreads = v; }
   else INS_FAIL(c, "unknown parameter: " + k);
   return 0;

@@ -7,7 +7,7 @@
 //
 // A block owns COLS consecutive columns c = ky*nxw + kx of the spectrum (contiguous in memory for every z)
 // and all nz points of each: the tile [nz][COLS] sits in shared memory.  Forward = in-place
-// decimation-in-frequency passes of radix 8/4/2 (natural order in, digit-reversed order out); the symbol
+// decimation-in-frequency passes of radix 16/8/4/2 (natural order in, digit-reversed order out); the symbol
 // is applied at digit-reversed positions; inverse = the adjoint passes in reverse order (digit-reversed in,
 // natural out).  No reordering pass, no second buffer.  Twiddles exp(-2 pi i t / nz) come from a table
 // computed in Float64 on the host.
@@ -86,10 +86,32 @@ template <typename T, bool INV> __device__ __forceinline__ void dft8(Cx<T> (&v)[
   v[2] = cadd(e[2], o2);   v[6] = csub(e[2], o2);
   v[3] = cadd(e[3], o3);   v[7] = csub(e[3], o3);
 }
+// 16 points as 4 x 4 (n = 4a + b, k = q1 + 4 q2):  w16^{nk} = w4^{a q1} * w16^{b q1} * w4^{b q2}
+template <typename T, bool INV> __device__ __forceinline__ void dft16(Cx<T> (&v)[16]) {
+  const T c1 = T(0.92387953251128675613), s1 = T(0.38268343236508977173), h = T(0.70710678118654752440);
+  // w16^k = exp(-2 pi i k / 16) for k = b * q1 (cmul<.., INV> multiplies by the conjugate for the inverse)
+  const Cx<T> w[10] = {{T(1), T(0)}, {c1, -s1}, {h, -h}, {s1, -c1}, {T(0), T(-1)}, {-s1, -c1}, {-h, -h}, {-c1, -s1}, {T(-1), T(0)}, {-c1, s1}};
+  Cx<T> t[4][4];  // t[b][q1]
+#pragma unroll
+  for (int b = 0; b < 4; b++) {
+    Cx<T> x[4] = {v[b], v[4 + b], v[8 + b], v[12 + b]};
+    dft4<T, INV>(x);
+#pragma unroll
+    for (int q1 = 0; q1 < 4; q1++) t[b][q1] = (b == 0 || q1 == 0) ? x[q1] : cmul<T, INV>(x[q1], w[b * q1]);
+  }
+#pragma unroll
+  for (int q1 = 0; q1 < 4; q1++) {
+    Cx<T> y[4] = {t[0][q1], t[1][q1], t[2][q1], t[3][q1]};
+    dft4<T, INV>(y);
+#pragma unroll
+    for (int q2 = 0; q2 < 4; q2++) v[q1 + 4 * q2] = y[q2];
+  }
+}
 template <typename T, int R, bool INV> __device__ __forceinline__ void dftR(Cx<T> (&v)[R]) {
   if constexpr (R == 2) dft2<T, INV>(v);
   else if constexpr (R == 4) dft4<T, INV>(v);
-  else dft8<T, INV>(v);
+  else if constexpr (R == 8) dft8<T, INV>(v);
+  else dft16<T, INV>(v);
 }
 
 // one in-place pass over the tile s[nz][COLS] for blocks of length L = R << lsub (sub-stride 1 << lsub).
@@ -97,7 +119,7 @@ template <typename T, int R, bool INV> __device__ __forceinline__ void dftR(Cx<T
 // All sizes are powers of two: index arithmetic is shifts and masks.
 template <typename T, int R, bool INV, int COLS>
 __device__ __forceinline__ void zpass(Cx<T> *s, const Cx<T> *tw, int nz, int lsub, int tid, int nt) {
-  constexpr int LR = R == 8 ? 3 : (R == 4 ? 2 : 1), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
+  constexpr int LR = R == 16 ? 4 : (R == 8 ? 3 : (R == 4 ? 2 : 1)), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
   const int sub = 1 << lsub, nw = (nz >> LR) << LC;
   int ltstep = 0;  // log2(nz / L)
   while ((R << lsub << ltstep) < nz) ltstep++;
@@ -134,7 +156,7 @@ template <> __device__ __forceinline__ float rcp_<float>(float x) { return __frc
 // `axy`, `zero_col` belong to the thread's column, which does not change over the loop (nt % COLS == 0).
 template <typename T, int R, int COLS>
 __device__ __forceinline__ void zpass_mid(Cx<T> *s, const T *azr, int nz, int tid, int nt, T axy, T negN, bool zero_col) {
-  constexpr int LR = R == 8 ? 3 : (R == 4 ? 2 : 1), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
+  constexpr int LR = R == 16 ? 4 : (R == 8 ? 3 : (R == 4 ? 2 : 1)), LC = COLS == 16 ? 4 : (COLS == 8 ? 3 : 2);
   const int nw = (nz >> LR) << LC;
 #pragma unroll 2
   for (int w = tid; w < nw; w += nt) {
@@ -159,7 +181,7 @@ __device__ __forceinline__ void zpass_mid(Cx<T> *s, const T *azr, int nz, int ti
 
 struct ZRadix {
   int n;        // number of passes
-  int r[12];    // log2 of the radices of the forward passes in order (3, 2 or 1)
+  int r[12];    // log2 of the radices of the forward passes in order (4 [Float32 only], 3, 2 or 1)
 };
 
 // twiddles and az-at-digit-reversed-positions tables of a block (all threads; followed by a barrier at the caller)
@@ -187,7 +209,8 @@ __device__ __forceinline__ void zsolve_tile(Cx<T> *s, const Cx<T> *tw, const T *
   int lL = lnz;  // log2 of the current block length
   for (int p = 0; p + 1 < rad.n; p++) {
     const int lr = rad.r[p];
-    if (lr == 3) zpass<T, 8, false, COLS>(s, tw, nz, lL - 3, tid, nt);
+    if (sizeof(T) == 4 && lr == 4) { if constexpr (sizeof(T) == 4) zpass<T, 16, false, COLS>(s, tw, nz, lL - 4, tid, nt); }
+    else if (lr == 3) zpass<T, 8, false, COLS>(s, tw, nz, lL - 3, tid, nt);
     else if (lr == 2) zpass<T, 4, false, COLS>(s, tw, nz, lL - 2, tid, nt);
     else zpass<T, 2, false, COLS>(s, tw, nz, lL - 1, tid, nt);
     lL -= lr;
@@ -195,7 +218,8 @@ __device__ __forceinline__ void zsolve_tile(Cx<T> *s, const Cx<T> *tw, const T *
   }
   {
     const int lr = rad.r[rad.n - 1];  // == lL
-    if (lr == 3) zpass_mid<T, 8, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
+    if (sizeof(T) == 4 && lr == 4) { if constexpr (sizeof(T) == 4) zpass_mid<T, 16, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col); }
+    else if (lr == 3) zpass_mid<T, 8, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
     else if (lr == 2) zpass_mid<T, 4, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
     else zpass_mid<T, 2, COLS>(s, azr, nz, tid, nt, axy, negN, zero_col);
     __syncthreads();
@@ -203,7 +227,8 @@ __device__ __forceinline__ void zsolve_tile(Cx<T> *s, const Cx<T> *tw, const T *
   // inverse: digit-reversed -> natural (adjoint passes in reverse order)
   for (int p = rad.n - 2; p >= 0; p--) {
     const int lr = rad.r[p];
-    if (lr == 3) zpass<T, 8, true, COLS>(s, tw, nz, lL, tid, nt);
+    if (sizeof(T) == 4 && lr == 4) { if constexpr (sizeof(T) == 4) zpass<T, 16, true, COLS>(s, tw, nz, lL, tid, nt); }
+    else if (lr == 3) zpass<T, 8, true, COLS>(s, tw, nz, lL, tid, nt);
     else if (lr == 2) zpass<T, 4, true, COLS>(s, tw, nz, lL, tid, nt);
     else zpass<T, 2, true, COLS>(s, tw, nz, lL, tid, nt);
     lL += lr;
