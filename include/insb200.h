@@ -209,13 +209,22 @@ int insb200_timers(insb200_ctx *ctx, const char **names, double *ms, long long *
 int insb200_reset_timers(insb200_ctx *ctx);
 
 /* Kernel variant switch for A/B runs: 0 = reference-structure kernels (one thread per cell,
- * direct global loads), 1 = tiled shared-memory kernels (default where available). */
+ * direct global loads), 1 = LDG-tiled shared-memory kernels, 2 = TMA plane-pipeline kernels (3-D;
+ * default).  Results are bit-identical across variants. */
 int insb200_set_variant(insb200_ctx *ctx, int variant);
 
-/* Tuning knobs for A/B runs (results are bit-identical for every setting):
- *   "variant" 0/1 (as above), "tile_y" 8|16 (cells per block in y of the tiled stage kernel),
- *   "zchunk" planes marched per block, "fuse_gradient" 0/1 (projection of stage i applied by the
- *   loader of stage i+1 instead of a gradient kernel). */
+/* Tuning knobs for A/B runs.  Unless noted, results are bit-identical for every setting.
+ *   stage kernels:  "variant" 0|1|2, "tile_y" 8|16, "zchunk" planes marched per block (0 = automatic),
+ *                   "fuse_gradient" 0|1 (projection of stage i applied by the loader of stage i+1),
+ *                   "stage_x2" 0|1|2 (packed-FP32 stage kernel: 1 exact, 2 contracted -- 2 differs by round-off),
+ *                   2-D: "fuse2d" 0|1 (warp-marching fused stage kernel), "rows2d" 0|1, "rows_chunk" rows per block
+ *   closure:        "smag_v" 1|2, "smag_ty" 8|16, "smag_zchunk"
+ *   Poisson solve:  "zsolve" 0|1 (fused last-axis kernel instead of cuFFT's z pass; differs from cuFFT by round-off),
+ *                   "zcols" 0|4|8|16, "zthreads", "zradix16" 0|1 (Float32 radix-16 passes; round-off),
+ *                   "fft_chunk" planes per cufftExec (0 = whole slab), "fft_pipe" / "fft_pipe_min_ranks"
+ *   multi-GPU:      "p2p" 0|1 (peer-store transposes over CUDA IPC; before the first solve), "p2p_halo" 0|1,
+ *                   "p2p_fused" 0|1|2
+ *   "graphs" 1|0|-1 (CUDA-graph replay of whole steps: on, off, automatic for slabs of <= 2^22 cells). */
 int insb200_set_param(insb200_ctx *ctx, const char *name, double value);
 
 /* Whole RK steps are replayed as CUDA graphs where that is possible (one rank, fixed dt, a non-default stream, timers
