@@ -751,6 +751,7 @@ static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T
   INS_TRY((zsolve_prepare<T>(c, rad)));
   const size_t col_bytes = (size_t)nz * sizeof(Cx<T>);
   if (c->zcols == 4) return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
+  if (c->zcols == 16 && 16 * col_bytes <= 131072) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);  // explicit request only
   if (c->zcols == 8 && 8 * col_bytes <= 131072) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
   if (16 * col_bytes <= 65536) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);
   if (8 * col_bytes <= 65536) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
