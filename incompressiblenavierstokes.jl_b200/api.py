@@ -153,7 +153,9 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
             raise AssertionError("B200 backend requires uniform grid spacing.")
         if n[a] % 2:
             raise AssertionError("B200 backend requires even number of volumes.")
-    Re = T(1000) if Re is None else T(Re)
+    if Re is None:  # setup.jl:12: Re = isnothing(temperature) ? 1000 : 1 / temperature.α1
+        Re = T(1000) if temperature is None else T(1) / T(temperature.alpha1)
+    Re = T(Re)
     xg = tuple(_padghost_periodic(xa).astype(T) for xa in x)
     h = tuple(T(np.diff(xa)[0]) for xa in xg)  # Delta[a][1]
     ctx = _Ctx(D, n, T, h, Re, backend)

@@ -32,6 +32,15 @@
 #undef REAL
 #undef SUF
 
+/* bench.py sets the thread count itself: torch.distributed.run exports OMP_NUM_THREADS=1 to its workers */
+void cpuref_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int cpuref_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();

@@ -38,11 +38,20 @@ def _load():
             fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double), C.c_double, C.c_double, C.c_int,
                            C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double, C.c_void_p, _CB]
         _lib.cpuref_num_threads.restype = C.c_int
+        _lib.cpuref_set_num_threads.argtypes = [C.c_int]
+        _lib.cpuref_set_num_threads.restype = None
     return _lib
 
 
 def num_threads():
     return int(_load().cpuref_num_threads())
+
+
+def set_num_threads(n):
+    """OpenMP threads of the C loops (the scipy.fft workers follow `workers=` of rk_steps).  Callers that want
+    all host cores must say so: torch.distributed.run exports OMP_NUM_THREADS=1 to its workers."""
+    _load().cpuref_set_num_threads(int(n))
+    return num_threads()
 
 
 def _psolver_inplace(setup, workers):
@@ -96,7 +105,7 @@ def rk_steps(u, setup, dt, nsteps, method, theta=None, workers=-1):
     return u
 
 
-def rk44_steps(u, setup, dt, nsteps, theta=None):
+def rk44_steps(u, setup, dt, nsteps, theta=None, workers=-1):
     from . import ins_oracle as o
 
-    return rk_steps(u, setup, dt, nsteps, o.RK44(setup.grid.T), theta)
+    return rk_steps(u, setup, dt, nsteps, o.RK44(setup.grid.T), theta, workers=workers)

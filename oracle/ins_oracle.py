@@ -124,7 +124,9 @@ def Setup(x, Re=None, bodyforce=None, issteadybodyforce=True, closure_model=None
     """
     grid = Grid(x)
     T = grid.T
-    Re = T(1000) if Re is None else T(Re)
+    if Re is None:  # setup.jl:12: Re = isnothing(temperature) ? 1000 : 1 / temperature.α1
+        Re = T(1000) if temperature is None else T(1) / T(temperature.alpha1)
+    Re = T(Re)
     setup = SimpleNamespace(
         grid=grid, Re=Re, bodyforce=bodyforce, issteadybodyforce=False,
         closure_model=closure_model, temperature=temperature,

@@ -47,6 +47,28 @@ def test_oracle_temperature_coefficients():
         assert np.isclose(q3.alpha1, q3.alpha3) and np.isclose(q3.gamma, 1)
 
 
+def test_oracle_default_Re_follows_temperature():
+    """setup.jl:12: without an explicit Re, `Re = 1 / temperature.α1`."""
+    for T in (np.float32, np.float64):
+        x = tuple(np.linspace(0.0, 1.0, 9).astype(T) for _ in range(2))
+        q = o.temperature_equation(T(0.71), T(1e6), T(0.1))
+        s = o.Setup(x, temperature=q)
+        assert s.Re.dtype == T and s.Re == T(1) / q.alpha1
+        assert o.Setup(x).Re == T(1000)
+
+
+@pytest.mark.gpu
+def test_mirror_default_Re_follows_temperature():
+    import insb200 as ins
+
+    T = np.float32
+    x = tuple(np.linspace(0.0, 1.0, 17).astype(T) for _ in range(2))
+    q = ins.temperature_equation(T(0.71), T(1e6), T(0.1))
+    sc = ins.Setup(x, temperature=q)
+    so = o.Setup(x, temperature=o.temperature_equation(T(0.71), T(1e6), T(0.1)))
+    assert sc.Re == so.Re == T(1) / T(q.alpha1)
+
+
 def test_mirror_temperature_equation_matches_oracle():
     """The host mirror forms the coefficients of setup.jl:56-86 exactly like the oracle (pure host code)."""
     import insb200 as ins
