@@ -12,9 +12,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libinsb200.so")
-SOURCES = [os.path.join(CSRC, "insb200.cu"), os.path.join(CSRC, "temperature.cu")]
+SOURCES = [os.path.join(CSRC, "insb200.cu"), os.path.join(CSRC, "temperature.cu"), os.path.join(CSRC, "fast.cu")]
+# translation units built WITH FMA contraction: the default (tolerance-parity) kernels; everything else keeps the
+# reference's operation order bit for bit (-fmad=false)
+CONTRACTED = {"fast.cu"}
 OBJDIR = os.path.join(HERE, "build")  # git-ignored object cache: only stale translation units are recompiled
-HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "stage2d.cuh", "zsolve.cuh")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "stage2d.cuh", "zsolve.cuh", "fast.cuh", "fast_stage.cuh")] + [
     os.path.join(os.path.dirname(HERE), "include", "insb200.h")
 ]
 
@@ -63,7 +66,8 @@ def build(force=False, verbose=False, extra_flags=()):
         objs.append(obj)
         if not force and not extra_flags and not _stale(obj, [src] + HEADERS + [os.path.abspath(__file__)]):
             continue
-        cmd = [nvcc] + NVCC_FLAGS + list(extra_flags) + ["-c", "-o", obj, src]
+        flags = [f for f in NVCC_FLAGS if not (os.path.basename(src) in CONTRACTED and f == "-fmad=false")]
+        cmd = [nvcc] + flags + list(extra_flags) + ["-c", "-o", obj, src]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd))

@@ -1,0 +1,85 @@
+// fast.cu -- the translation unit of the contracted-arithmetic kernels (built WITHOUT -fmad=false, see build.py).
+// insb200.cu keeps the reference's operation order bit for bit (-fmad=false) and stays the home of every kernel an
+// operator-level parity test compares with the oracle; the kernels here are the shipped default of the 3-D time step,
+// whose parity bar is north_star's tolerance after RK steps (rel-L2 <= 1e-5 Float32 / 1e-12 Float64).
+#include <type_traits>
+
+#include "fast.cuh"
+#include "fast_stage.cuh"
+
+namespace insb200 {
+
+#define CHECK_LAUNCH(c)                      \
+  do {                                       \
+    (c)->launches++;                         \
+    INS_CUDA((c), cudaGetLastError());       \
+  } while (0)
+
+bool stage_fast_supported(const insb200_ctx *c, bool smag) {
+  if (c->D != 3 || !c->padded || c->exact) return false;
+  if (c->nloc[0] % 32 || c->nloc[1] % 16 || c->nloc[2] < 2) return false;
+  if (c->dtype == INSB200_F64 && smag) return false;  // the sigma ring of a Float64 tile does not fit next to 8 plane slots
+  return true;
+}
+
+template <typename T>
+static FastK<T> make_fastk(const insb200_ctx *c, double theta) {
+  FastK<T> K;
+  const T visc = T(1) / T(c->Re);
+  T d2 = T(0);
+  for (int a = 0; a < 3; a++) {
+    const T rh = T(1) / T(c->h[a]);
+    K.rh[a] = rh;
+    K.vrr[a] = visc * rh * rh;
+    K.q[a] = T(0.25) * rh;
+    d2 += T(c->h[a]) * T(c->h[a]);
+  }
+  K.vol = T(c->h[0]) * T(c->h[1]) * T(c->h[2]);
+  const T th = std::isnan(theta) ? T(0) : T(theta);
+  K.e2c = T(2) * (th * th) * d2;  // 2 theta^2 d^2 (operators.jl:1128, 1146-1148)
+  return K;
+}
+
+template <typename T, bool PG, bool SM, bool GEN>
+static int launch_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double theta, const void *ubase, const void *pbase) {
+  typedef FastCfg<T, SM> Cfg;
+  CUtensorMap tu, tp;
+  INS_TRY(get_tmap(c, ubase, 3, Cfg::BX, Cfg::BY, &tu));
+  INS_TRY(get_tmap(c, pbase, 1, Cfg::BX, Cfg::BYP, &tp));
+  const int tiles = (c->nloc[0] / Cfg::TX) * (c->nloc[1] / Cfg::TY);
+  const int bps = (SM || sizeof(T) == 8) ? 1 : 2;
+  const int zc = auto_zchunk(c, c->zchunk, tiles, bps, -Cfg::R0);
+  auto kern = k_stage3d_fast<T, PG, SM, GEN>;
+  static int attr_dev = -1;  // per device: a second context on another device needs its own opt-in
+  if (attr_dev != c->device) {
+    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+    attr_dev = c->device;
+  }
+  dim3 grd(c->nloc[0] / Cfg::TX, c->nloc[1] / Cfg::TY, (c->nloc[2] + zc - 1) / zc), blk(Cfg::TX, Cfg::NTY, 1);
+  kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, a, make_fastk<T>(c, theta), g, zc, c->org[0], c->org[1], c->org[2]);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+
+template <typename T>
+int launch_stage_fast(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double theta, const void *ubase, const void *pbase) {
+  const bool smag = !std::isnan(theta);
+  if (!stage_fast_supported(c, smag) || a.nk > 3) INS_FAIL(c, "launch_stage_fast: unsupported configuration (caller must check)");
+  const bool gen = a.nk > 0 || a.kout[0] == nullptr;
+  const void *pb = pbase ? pbase : c->preal;  // first stage: a valid descriptor, never read
+#define LSF(PG, SM, GEN) launch_i<T, PG, SM, GEN>(c, a, g, theta, ubase, pb)
+  if constexpr (std::is_same<T, float>::value) {
+    if (smag) {
+      if (pbase) return gen ? LSF(true, true, true) : LSF(true, true, false);
+      return gen ? LSF(false, true, true) : LSF(false, true, false);
+    }
+  }
+  if (pbase) return gen ? LSF(true, false, true) : LSF(true, false, false);
+  return gen ? LSF(false, false, true) : LSF(false, false, false);
+#undef LSF
+}
+
+template int launch_stage_fast<float>(insb200_ctx *, const TmaStageArgs<float> &, Geo, double, const void *, const void *);
+template int launch_stage_fast<double>(insb200_ctx *, const TmaStageArgs<double> &, Geo, double, const void *, const void *);
+
+}  // namespace insb200

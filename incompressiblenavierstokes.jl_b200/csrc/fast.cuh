@@ -1,0 +1,21 @@
+// fast.cuh -- host interface between insb200.cu (compiled with -fmad=false: the bit-exact kernels) and fast.cu
+// (compiled with FMA contraction: the default kernels of the 3-D step).
+#pragma once
+#include "tiled.cuh"
+#include "tma_stage.cuh"
+
+namespace insb200 {
+
+// insb200.cu
+int get_tmap(insb200_ctx *c, const void *base, int nc, int box_x, int box_y, CUtensorMap *out);
+int auto_zchunk(const insb200_ctx *c, int user, int tiles, int blocks_per_sm, int extra);
+
+// fast.cu: one RK stage up to the Poisson right-hand side with k_stage3d_fast (fast_stage.cuh).
+// theta = NaN: no closure.  ubase / pbase: START of the padded velocity / multiplier buffers (pbase == nullptr:
+// first stage, no projection on load).  The caller checks stage_fast_supported() and that the tableau row reads at
+// most 3 earlier k_j (a.nk <= 3); everything else takes the exact kernels of insb200.cu.
+template <typename T>
+int launch_stage_fast(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double theta, const void *ubase, const void *pbase);
+bool stage_fast_supported(const insb200_ctx *c, bool smag);
+
+}  // namespace insb200

@@ -14,6 +14,7 @@
 #include "tma_stage_x2.cuh"
 #include "stage2d.cuh"
 #include "zsolve.cuh"
+#include "fast.cuh"
 
 namespace insb200 {
 thread_local std::string g_create_error;
@@ -560,7 +561,7 @@ typedef CUresult (*PFN_tmap_encode)(CUtensorMap *, CUtensorMapDataType, cuuint32
                                     CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 // descriptor of a padded buffer with nc components, box = (box_x, box_y, 1, nc)
-static int get_tmap(insb200_ctx *c, const void *base, int nc, int box_x, int box_y, CUtensorMap *out) {
+int get_tmap(insb200_ctx *c, const void *base, int nc, int box_x, int box_y, CUtensorMap *out) {
   auto key = std::make_tuple(base, nc, box_y);
   auto it = c->tmaps.find(key);
   if (it != c->tmaps.end()) { *out = it->second; return 0; }
@@ -1485,7 +1486,7 @@ static const int kNS = 5;  // velocity plane slots of the stage kernel (prefetch
 // a block costs zc planes plus `extra` planes of pipeline prologue, and the grid runs in rounds of resident blocks.
 // Measured against a sweep (tools/sweep_zchunk.sh): 128^3 Float64 stage kernel 64 planes -> 32: 0.112 -> 0.063 ms
 // (64 blocks left 84 of 148 SMs idle); 512^3 closure kernel 128 -> 256: 1.89 -> 1.86 ms.
-static int auto_zchunk(const insb200_ctx *c, int user, int tiles, int blocks_per_sm, int extra) {
+int auto_zchunk(const insb200_ctx *c, int user, int tiles, int blocks_per_sm, int extra) {
   const int nz = c->nloc[2];
   if (user > 0) return std::max(2, std::min(user, nz));
   int best = nz;
@@ -1681,7 +1682,6 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
   const Rh<T> rh = make_rh<T>(c);
   const i64 goff = c->corg;
   const bool multi = c->nranks > 1;
-  if (smag) INS_TRY(ensure_vec(c, &c->sbuf));
   INS_TRY(dev_alloc(c, &c->preal2, (size_t)c->ccomp * sizeof(T)));
   INS_TRY((fill_ghosts<T>(c, c->ubuf[0], 3, 2, 2)));  // apply_bc_u! before momentum (:19)
   int cur = 0;
@@ -1694,13 +1694,20 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
       std::swap(c->preal, c->preal2);  // p of the previous stage -> preal2; preal receives the new right-hand side
       pbase = c->preal2;
     }
-    if (smag) INS_TRY((launch_smag_tma<T>(c, theta, c->ubuf[cur], pbase)));
+    int nkrow = 0;  // earlier stage derivatives this tableau row reads
+    for (int j = 0; j < i; j++) nkrow += tb.A[i * tb.s + j] != 0.0;
+    // fused closure + stage kernel (fast.cu) for rows with at most 3 earlier k_j; `exact` and longer rows keep the two kernels below
+    const bool fast = stage_fast_supported(c, smag) && nkrow <= 3;
+    if (smag && !fast) {
+      INS_TRY(ensure_vec(c, &c->sbuf));
+      INS_TRY((launch_smag_tma<T>(c, theta, c->ubuf[cur], pbase)));
+    }
     TmaStageArgs<T> a;
     memset(&a, 0, sizeof a);
     for (int q = 0; q < 3; q++) {
       const i64 co = goff + q * c->ccomp;
       a.u0[q] = (const T *)c->ubuf[0] + co;
-      a.sadd[q] = smag ? (const T *)c->sbuf + co : nullptr;
+      a.sadd[q] = (smag && !fast) ? (const T *)c->sbuf + co : nullptr;
       a.force[q] = c->force ? (const T *)c->force + co : nullptr;
       a.kout[q] = tb.need[i] ? (T *)c->kbuf[i] + co : nullptr;
       a.unew[q] = (T *)c->ubuf[nxt] + co;
@@ -1717,7 +1724,8 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
     a.sy = c->csy; a.sz = c->csz; a.sc = c->ccomp;
     {
       ScopedTimer tm(c, (a.nk > 0 || !a.kout[0]) ? TM_STAGE_GEN : TM_STAGE);
-      INS_TRY((launch_stage_tma<T>(c, a, g, visc, rh, c->ubuf[cur], pbase)));
+      if (fast) INS_TRY((launch_stage_fast<T>(c, a, g, theta, c->ubuf[cur], pbase)));
+      else INS_TRY((launch_stage_tma<T>(c, a, g, visc, rh, c->ubuf[cur], pbase)));
     }
     // apply_bc_u! (:48): ghosts of u' for the next stage's boxes (and, multi-rank, for the first plane's divergence)
     if (!last) INS_TRY((fill_ghosts<T>(c, c->ubuf[nxt], 3, 2, 2)));
@@ -2108,6 +2116,7 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   const int v = (int)value;
   clear_graphs(c);  // a captured step holds the launch configuration of the parameters it was captured with
   if (k == "variant") c->variant = v;
+  else if (k == "exact") c->exact = v != 0;   // 1: bit-exact kernels (reference operation order, no contraction); 0: fast kernels (fast.cu)
   else if (k == "graphs") c->use_graphs = v;  // 1 on, 0 off, -1 automatic (small grids)
   else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
   else if (k == "zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "zchunk must be 0 (automatic) or >= 2"); c->zchunk = v; }

@@ -612,7 +612,7 @@ __global__ void k_reduce_partials(View<const T> u, Geo g, T vol, double *part_ke
 }
 
 // out[0] = sum part_ke ; out[1..3] = max part_max   (single block, fixed order -> deterministic)
-__global__ void k_reduce_final(const double *part_ke, const double *part_max, i64 nb, double *out) {
+static __global__ void k_reduce_final(const double *part_ke, const double *part_max, i64 nb, double *out) {
   double ke = 0.0, m0 = 0.0, m1 = 0.0, m2 = 0.0;
   for (i64 b = threadIdx.x; b < nb; b += blockDim.x) {
     ke += part_ke[b];

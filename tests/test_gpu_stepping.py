@@ -219,6 +219,7 @@ def test_kernel_variants_bit_identical(T, smag):
     u0 = o.random_field(so, kp=4, rng=np.random.default_rng(12))
     m = ins.RKMethods.RK44(T=T)
     results = {}
+    set_param(sc, "exact", 1)  # the bit-exact kernels; the fast kernels (fast.cu) are compared in tests/test_gpu_fast.py
     for name, params in [("naive", dict(variant=0)),
                          ("tiled16", dict(variant=1, tile_y=16, zchunk=64, fuse_gradient=1)),
                          ("tiled8_zc16", dict(variant=1, tile_y=8, zchunk=16, fuse_gradient=1)),

@@ -38,6 +38,7 @@ def main():
     dt = 2.5e-4 * 512 / max(n)
 
     def run(variant):
+        setup.ctx.call("insb200_set_param", b"exact", 1.0)  # bit-exact kernels on both sides
         setup.ctx.call("insb200_set_variant", variant)
         u = bench.synthetic_field(ins, setup)
         setup.ctx.call("insb200_reset_timers")
