@@ -474,7 +474,11 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
     else:
         u = synthetic_field(ins, setup, amp=amp)
         init = "24 random Fourier modes with Orlandi-type amplitudes evaluated per slab, projected on the device (the random_field spectrum needs the global grid on one device)"
-    dt = wl["dt"] * wl["n"] / base_n
+    # fixed step for the throughput run: the configured one, capped at half the reference's own CFL bound
+    # (get_cfl_timestep!, solver.jl:101-125) of the start field -- random_field(A = 1, kp = 10) reaches |u| = 16, for which
+    # the examples step adaptively; throughput does not depend on dt
+    dt_cfl = 0.5 * float(ins.get_cfl_timestep_(None, u, setup))
+    dt = min(wl["dt"] * wl["n"] / base_n, dt_cfl)
     lib, h = setup.ctx.lib, setup.ctx.h
     K, W = args.steps, args.warmup
     cells = float(np.prod([float(m) for m in n]))

@@ -80,6 +80,7 @@ struct insb200_ctx {
   int device = 0;
   int rank = 0, nranks = 1;
   int exact = 0;           // param "exact": 1 = the bit-exact kernels of insb200.cu everywhere; 0 = fast.cu's contracted kernels where they exist
+  int fast_gen = 0;        // param "fast_gen": without closure, tableau rows that read earlier k_j (RK44's last row): 1 = k_stage3d_fast<GEN> (one block per SM, 128 registers), 0 = the exact TMA kernel (measured faster)
   int variant = 2;         // 0: one thread per cell, 1: LDG-tiled stage kernel, 2: TMA plane pipeline (3-D)
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
   int fft_pipe = 4;        // param: nranks > 1, peer transposes: the slab is transformed in this many z-chunks and the scatter of

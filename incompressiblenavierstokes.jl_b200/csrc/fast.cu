@@ -47,7 +47,7 @@ static int launch_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double thet
   INS_TRY(get_tmap(c, ubase, 3, Cfg::BX, Cfg::BY, &tu));
   INS_TRY(get_tmap(c, pbase, 1, Cfg::BX, Cfg::BYP, &tp));
   const int tiles = (c->nloc[0] / Cfg::TX) * (c->nloc[1] / Cfg::TY);
-  const int bps = (SM || sizeof(T) == 8) ? 1 : 2;
+  const int bps = (SM || GEN || sizeof(T) == 8) ? 1 : 2;
   const int zc = auto_zchunk(c, c->zchunk, tiles, bps, -Cfg::R0);
   auto kern = k_stage3d_fast<T, PG, SM, GEN>;
   static int attr_dev = -1;  // per device: a second context on another device needs its own opt-in
@@ -65,7 +65,7 @@ template <typename T>
 int launch_stage_fast(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double theta, const void *ubase, const void *pbase) {
   const bool smag = !std::isnan(theta);
   if (!stage_fast_supported(c, smag) || a.nk > 3) INS_FAIL(c, "launch_stage_fast: unsupported configuration (caller must check)");
-  const bool gen = a.nk > 0 || a.kout[0] == nullptr;
+  const bool gen = a.nk > 0 || a.kout[0] == nullptr || a.force[0] != nullptr;  // the general kernels also carry the stored body force
   const void *pb = pbase ? pbase : c->preal;  // first stage: a valid descriptor, never read
 #define LSF(PG, SM, GEN) launch_i<T, PG, SM, GEN>(c, a, g, theta, ubase, pb)
   if constexpr (std::is_same<T, float>::value) {

@@ -63,11 +63,11 @@ struct FastCfg {
   static constexpr int UPL = BY * BX;
   static constexpr int USLOT = ((3 * UPL * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
   static constexpr int PSLOT = ((BYP * BX * (int)sizeof(T) + 127) / 128) * 128 / (int)sizeof(T);
-  static constexpr int NS = SMAG ? 8 : 5, NPS = NS + 1;
+  static constexpr int NS = 8, NPS = 8, NG = 4;  // ring sizes: velocity planes, pressure planes, sigma planes (powers of two, see FsOffs)
   static constexpr int POFF = NS * USLOT;
   static constexpr int SX = TX + 2, SY = TY + 2, SPL = SX * SY, SSLOT = 6 * SPL;  // sigma tile: p-cells -1 .. TX / TY
   static constexpr int SOFF = POFF + NPS * PSLOT;
-  static constexpr int DOFF = SOFF + (SMAG ? 3 * SSLOT : 0);  // divergence staging: [2][TY][TX+1] + [2][TY+1][TX]
+  static constexpr int DOFF = SOFF + (SMAG ? NG * SSLOT : 0);  // divergence staging: [2][TY][TX+1] + [2][TY+1][TX]
   static constexpr int DXN = TY * (TX + 1), DYN = (TY + 1) * TX;
   static constexpr int ELEMS = DOFF + 2 * DXN + 2 * DYN;
   static constexpr size_t SMEM = 128 + (size_t)ELEMS * sizeof(T) + 8 * NS + 16;
@@ -101,20 +101,52 @@ struct FsHalo {      // a halo point (one component): lower z-face flux and the 
   T fz, s0, sm;
 };
 
+// sqrt for the eddy viscosity: x * rsqrt(x) (2 instructions on the device instead of the 9 of the IEEE sequence;
+// relative error 2^-22, far inside the parity tolerance)
+FS_HD float fs_sqrt(float x) {
+#if defined(__CUDA_ARCH__)
+  return x * rsqrtf(fmaxf(x, 1e-37f));
+#else
+  return sqrtf(x);
+#endif
+}
+FS_HD double fs_sqrt(double x) { return sqrt(x); }
+
 template <typename T>
 FS_HD void fs_zero(T *p, int n) {
   for (int i = 0; i < n; i++) p[i] = T(0);
 }
 
 // ---- phase A: u(plane) = u'(plane) - grad p over the whole box ---------------------------------------------------
-// (the last column / row of the box is never consumed, so p[l+1], p[l+BX] may run into the next row / the extra p row)
+// 16 bytes (V elements) per thread and access: box rows are multiples of 16 B, so a plane is UPL / V vectors and the
+// neighbours p(+y), p(+z) of a vector are vectors again; p(+x) needs one more scalar.  (The last column / row of the
+// box is never consumed, so p[l+1] / p[l+BX] may run into the next row / the extra row of the pressure box.)
+template <typename T>
+struct alignas(16) FsVec {
+  T v[16 / sizeof(T)];
+};
+// Thread `pt` of `np` projecting threads takes the vectors pt, pt + np, ...
 template <typename T, typename Cfg>
-FS_HD void fs_project(T *u, const T *p, const T *p1, int tid, const T (&rh)[3]) {
-  for (int l = tid; l < Cfg::UPL; l += Cfg::NT) {
-    const T p0 = p[l];
-    u[l] = u[l] - (p[l + 1] - p0) * rh[0];
-    u[Cfg::UPL + l] = u[Cfg::UPL + l] - (p[l + Cfg::BX] - p0) * rh[1];
-    u[2 * Cfg::UPL + l] = u[2 * Cfg::UPL + l] - (p1[l] - p0) * rh[2];
+FS_HD void fs_project(T *u, const T *p, const T *p1, int pt, int np, const T (&rh)[3]) {
+  constexpr int V = Cfg::V, NV = Cfg::UPL / V;
+  static_assert(Cfg::UPL % V == 0 && Cfg::BX % V == 0, "box rows are whole vectors");
+  typedef FsVec<T> Vec;
+  for (int l = pt; l < NV; l += np) {
+    const Vec p0 = reinterpret_cast<const Vec *>(p)[l];
+    const Vec py = reinterpret_cast<const Vec *>(p)[l + Cfg::BX / V];
+    const Vec pz = reinterpret_cast<const Vec *>(p1)[l];
+    const T pn = p[l * V + V];
+    Vec ux = reinterpret_cast<Vec *>(u)[l], uy = reinterpret_cast<Vec *>(u + Cfg::UPL)[l], uz = reinterpret_cast<Vec *>(u + 2 * Cfg::UPL)[l];
+#pragma unroll
+    for (int i = 0; i < V; i++) {
+      const T px = i + 1 < V ? p0.v[i + 1 < V ? i + 1 : 0] : pn;
+      ux.v[i] = ux.v[i] - (px - p0.v[i]) * rh[0];
+      uy.v[i] = uy.v[i] - (py.v[i] - p0.v[i]) * rh[1];
+      uz.v[i] = uz.v[i] - (pz.v[i] - p0.v[i]) * rh[2];
+    }
+    reinterpret_cast<Vec *>(u)[l] = ux;
+    reinterpret_cast<Vec *>(u + Cfg::UPL)[l] = uy;
+    reinterpret_cast<Vec *>(u + 2 * Cfg::UPL)[l] = uz;
   }
 }
 
@@ -140,7 +172,7 @@ FS_HD void fs_sigma(FsSig<T> &s, const T *M, const T *Tq, T *out, int rB, const 
       const T sxz2 = gxz * K.q[2] + gzx * K.q[0];
       const T syz2 = gyz * K.q[2] + gzy * K.q[1];
       const T ss = (sxx * sxx + syy * syy + szz * szz) + T(0.5) * (sxy2 * sxy2 + sxz2 * sxz2 + syz2 * syz2);
-      const T e2 = K.e2c * sqrt(T(2) * ss);         // 2 nu_t
+      const T e2 = K.e2c * fs_sqrt(T(2) * ss);      // 2 nu_t
       const T eh = T(0.5) * e2;
       out[0] = e2 * sxx;
       out[SPL] = eh * sxy2;
@@ -281,13 +313,59 @@ FS_HD int fs_wrap(int i, int n, int wrap) {
   return i < 0 ? i + n : (i >= n ? i - n : i);
 }
 
+// Block-uniform shared-memory offsets (elements) of the planes one iteration touches.  Velocity plane q lives in slot
+// q mod 8, pressure plane q in slot q mod 8, sigma plane rB in slot rB mod 4, the staging rows alternate.  With r the
+// iteration (stencil plane), q = r + 2:
+//   u_mid / u_top  velocity planes r, r+1 (stencil)      u_bm / u_bt  velocity planes r+2, r+3 (sigma)
+//   u_a            velocity plane r + LEAD (projected)    p_a / p_b    its pressure planes q_A, q_A + 1
+//   g_w            sigma plane r+2 (written)              g_m / g_t    sigma planes r, r+1 (read)
+// make(r): general form (start-up and tail iterations).  steady<J>(H, HP): r = 4 g + J inside the 4x unrolled steady
+// loop -- every offset is an IMMEDIATE plus or minus H = (g & 1) * 4 * USLOT (HP likewise for the pressure ring),
+// because (c + 4 g) mod 8 = c xor 4 (g & 1): the loop carries two uniform registers instead of ten slot counters.
+template <typename Cfg>
+struct FsOffs {
+  int u_mid, u_top, u_bm, u_bt, u_a, p_a, p_b, g_w, g_m, g_t, stg;
+  static FS_HD FsOffs make(int r) {
+    FsOffs o;
+    const int q = r + 2 + 8;  // >= 0 for every r >= R0
+    o.u_mid = (q & 7) * Cfg::USLOT;
+    o.u_top = ((q + 1) & 7) * Cfg::USLOT;
+    o.u_bm = ((q + 2) & 7) * Cfg::USLOT;
+    o.u_bt = ((q + 3) & 7) * Cfg::USLOT;
+    o.u_a = ((q + Cfg::LEAD) & 7) * Cfg::USLOT;
+    o.p_a = Cfg::POFF + ((q + Cfg::LEAD) & 7) * Cfg::PSLOT;
+    o.p_b = Cfg::POFF + ((q + Cfg::LEAD + 1) & 7) * Cfg::PSLOT;
+    o.g_w = Cfg::SOFF + ((r + 2 + 8) & 3) * Cfg::SSLOT;
+    o.g_m = Cfg::SOFF + ((r + 8) & 3) * Cfg::SSLOT;
+    o.g_t = Cfg::SOFF + ((r + 1 + 8) & 3) * Cfg::SSLOT;
+    o.stg = Cfg::DOFF + (r & 1) * Cfg::DXN;
+    return o;
+  }
+  template <int J>
+  static FS_HD FsOffs steady(const int H, const int HP) {
+    FsOffs o;
+    constexpr int c0 = (2 + J) & 7, c1 = (3 + J) & 7, c2 = (4 + J) & 7, c3 = (5 + J) & 7, ca = (2 + J + Cfg::LEAD) & 7, cb = (3 + J + Cfg::LEAD) & 7;
+    o.u_mid = c0 * Cfg::USLOT + (c0 < 4 ? H : -H);
+    o.u_top = c1 * Cfg::USLOT + (c1 < 4 ? H : -H);
+    o.u_bm = c2 * Cfg::USLOT + (c2 < 4 ? H : -H);
+    o.u_bt = c3 * Cfg::USLOT + (c3 < 4 ? H : -H);
+    o.u_a = ca * Cfg::USLOT + (ca < 4 ? H : -H);
+    o.p_a = Cfg::POFF + ca * Cfg::PSLOT + (ca < 4 ? HP : -HP);
+    o.p_b = Cfg::POFF + cb * Cfg::PSLOT + (cb < 4 ? HP : -HP);
+    o.g_w = Cfg::SOFF + ((J + 2) & 3) * Cfg::SSLOT;
+    o.g_m = Cfg::SOFF + (J & 3) * Cfg::SSLOT;
+    o.g_t = Cfg::SOFF + ((J + 1) & 3) * Cfg::SSLOT;
+    o.stg = Cfg::DOFF + (J & 1) * Cfg::DXN;
+    return o;
+  }
+};
+
 template <typename T, bool PGRAD, bool SMAG, bool GEN>
 struct FsThread {
   typedef FastCfg<T, SMAG> Cfg;
   static constexpr int TX = Cfg::TX, TY = Cfg::TY, NT = Cfg::NT, BX = Cfg::BX, UPL = Cfg::UPL, XL = Cfg::XL;
-  static constexpr int NS = Cfg::NS, NPS = Cfg::NPS, USLOT = Cfg::USLOT, PSLOT = Cfg::PSLOT, POFF = Cfg::POFF;
-  static constexpr int SX = Cfg::SX, SPL = Cfg::SPL, SSLOT = Cfg::SSLOT, SOFF = Cfg::SOFF, DOFF = Cfg::DOFF;
-  static constexpr int LEAD = Cfg::LEAD, R0 = Cfg::R0;
+  static constexpr int SX = Cfg::SX, SY = Cfg::SY, SPL = Cfg::SPL, DOFF = Cfg::DOFF;
+  static constexpr int LEAD = Cfg::LEAD;
   static constexpr bool U0TILE = !PGRAD;
   static constexpr int NKP = GEN ? 3 : 1;  // earlier k_j prefetched in registers (RK44's last row has 3)
 
@@ -296,14 +374,15 @@ struct FsThread {
   const TmaStageArgs<T> *A;
   const FastK<T> *K;
   int kbeg, nk, n2, wrap2, qlast;
-  bool has_force, has_kout, have_prev;
+  bool has_force, has_kout, have_prev;  // force and "k_i not stored" only exist in the GEN kernels (the host picks them)
   int nkin;
   size_t szb;
   // roles and offsets
-  int tid, tx, ty;
+  int tid;
   bool cell_thr, hx, hy, hany, sig_thr;
-  int ha, hlx, hly, c_own, c_halo, c_sigu, c_sig, c_sigh;
-  size_t ocell, ohalo, ob, obh;
+  int ha, c_own, c_halo, c_sigu, c_sigw, c_sig, c_sigh;
+  int d_own_x, d_own_y, d_halo;  // staging rows: this cell's u'_x / u'_y entries; the halo thread's entry
+  size_t ob, obh;  // byte offsets of this thread's cell / halo point in plane max(r, 0)
   // march state
   FsCell<T> cs;
   FsCellSg<T> cg;
@@ -311,47 +390,50 @@ struct FsThread {
   FsHalo<T> hs;
   T un[3];
   T n_u0[3], n_f[3], n_k[3][NKP], nh_u0, nh_f, nh_k[NKP];
-  // slots, advanced by one per iteration (no division in the loop)
-  int sq_mid;        // slot of velocity plane r (q = r + 2)
-  int sa, sp_a;      // velocity slot (= barrier) and pressure slot of plane qA = r + LEAD + 2
-  uint32_t pa_par;   // phase parity of that barrier use
-  int sg_w;          // sigma ring slot written at this iteration (plane r + 2)
 
-  static FS_HD int inc(int s, int n) { return s + 1 == n ? 0 : s + 1; }
-  static FS_HD int add(int s, int d, int n) { const int t = s + d; return t >= n ? t - n : t; }
   FS_HD size_t plane_off(int r) const { return (size_t)(r < 0 ? fs_wrap(kbeg + r, n2, wrap2) : kbeg + r) * szb; }
 
-  FS_HD void init(T *su_, const TmaStageArgs<T> *A_, const FastK<T> *K_, const Geo &g, int zc, int tid_, int bx_, int by_, int bz_) {
+  // `warp`: the warp index of this thread, handed in as a WARP-UNIFORM value (device: read from lane 0 by a shuffle),
+  // so that every role test below is a uniform branch
+  FS_HD void init(T *su_, const TmaStageArgs<T> *A_, const FastK<T> *K_, const Geo &g, int zc, int tid_, int warp, int bx_, int by_, int bz_) {
     su = su_; A = A_; K = K_;
-    tid = tid_; ty = tid / TX; tx = tid - ty * TX;
+    tid = tid_;
+    const int lane = tid & 31;
+    const int ty = warp, tx = lane;  // TX == 32: a warp is one row of the tile
     const int i0 = bx_ * TX, j0 = by_ * TY;
     kbeg = bz_ * zc;
     nk = zc < g.n[2] - kbeg ? zc : g.n[2] - kbeg;
     n2 = g.n[2]; wrap2 = g.wrap[2];
     qlast = nk + (SMAG ? 3 : 2);
-    has_force = A->force[0] != nullptr;
+    has_force = GEN && A->force[0] != nullptr;
     has_kout = !GEN || A->kout[0] != nullptr;
     nkin = GEN ? A->nk : 0;
     szb = (size_t)A->sz * sizeof(T);
     have_prev = kbeg > 0 || g.wrap[2];  // otherwise plane 0's divergence is completed by k_divergence_planes
-    cell_thr = ty < TY;
+    cell_thr = warp < TY;
     const int hw = SMAG ? 16 : 1;  // warp of the x-halo; the y-halo is the next one
-    hx = tid >= 32 * hw && tid < 32 * hw + TY;
-    hy = tid >= 32 * (hw + 1) && tid < 32 * (hw + 2);
+    hx = warp == hw && lane < TY;
+    hy = warp == hw + 1;
     hany = hx || hy;
-    hlx = hx ? -1 : tid - 32 * (hw + 1);
-    hly = hx ? tid - 32 * hw : -1;
+    const int hlx = hx ? -1 : lane, hly = hx ? lane : -1;
     ha = hx ? 0 : 1;
     c_own = (ty + 2) * BX + tx + XL;
     c_halo = hany ? (hly + 2) * BX + hlx + XL : c_own;
-    ocell = ((size_t)(j0 + ty) * A->sy + (i0 + tx)) * sizeof(T);
+    const size_t ocell = ((size_t)(j0 + ty) * A->sy + (i0 + tx)) * sizeof(T);
     const int hgi = fs_wrap(i0 + hlx, g.n[0], 1), hgj = fs_wrap(j0 + hly, g.n[1], 1);
-    ohalo = hany ? ((size_t)hgj * A->sy + hgi) * sizeof(T) : ocell;
+    const size_t ohalo = hany ? ((size_t)hgj * A->sy + hgi) * sizeof(T) : ocell;
+    // sigma tile (SX x SY p-cells, x = -1 .. TX, y = -1 .. TY): warps 0 .. SY-1 own the columns 0 .. 31 of one row each
+    // (conflict-free rows), the two remaining columns of all rows go to the next 2 SY threads
+    int slx = lane, sly = warp;
+    if (warp >= SY) { const int e = tid - 32 * SY; sly = e >> 1; slx = 32 + (e & 1); }
     sig_thr = SMAG && tid < SPL;
-    const int sly = tid / SX, slx = tid - sly * SX;
     c_sigu = sig_thr ? (sly + 1) * BX + slx - 1 + XL : BX + XL;  // p-cell (slx-1, sly-1) in the velocity box
-    c_sig = (ty + 1) * SX + tx + 1;                              // this thread's cell in the sigma tile
+    c_sigw = sig_thr ? sly * SX + slx : 0;                        // ... and in the sigma tile
+    c_sig = (ty + 1) * SX + tx + 1;                               // this thread's cell in the sigma tile
     c_sigh = hany ? (hly + 1) * SX + hlx + 1 : c_sig;
+    d_own_x = ty * (TX + 1) + tx + 1;
+    d_own_y = 2 * Cfg::DXN + (ty + 1) * TX + tx;
+    d_halo = hx ? hly * (TX + 1) : 2 * Cfg::DXN + hlx;
     fs_zero(reinterpret_cast<T *>(&cs), (int)(sizeof(cs) / sizeof(T)));
     fs_zero(reinterpret_cast<T *>(&cg), (int)(sizeof(cg) / sizeof(T)));
     fs_zero(reinterpret_cast<T *>(&sg), (int)(sizeof(sg) / sizeof(T)));
@@ -362,39 +444,40 @@ struct FsThread {
     }
     nh_u0 = nh_f = T(0);
     for (int q = 0; q < NKP; q++) nh_k[q] = T(0);
-    sq_mid = ((R0 + 2) % NS + NS) % NS;
-    sa = 0; sp_a = 0; pa_par = 0; sg_w = 0;
     ob = plane_off(0) + ocell;
     obh = plane_off(0) + ohalo;
-    if (have_prev) fetch_operands(plane_off(-1) + ocell, plane_off(-1) + ohalo);
+    if (have_prev) {
+      if (cell_thr) fetch_operands<true, !SMAG>(plane_off(-1) + ocell, plane_off(-1) + ohalo);
+      else fetch_operands<false, SMAG>(plane_off(-1) + ocell, plane_off(-1) + ohalo);
+    }
   }
 
   // global operands (ustart, force, earlier k_j) of one plane into registers
+  template <bool CELL, bool HALO>
   FS_HD void fetch_operands(const size_t o1, const size_t o1h) {
-    if (cell_thr) {
+    if (CELL) {
 #pragma unroll
       for (int a = 0; a < 3; a++) {
         if (!U0TILE) n_u0[a] = fs_ld(A->u0[a], o1);
-        if (has_force) n_f[a] = fs_ld(A->force[a], o1);
+        if (GEN && has_force) n_f[a] = fs_ld(A->force[a], o1);
 #pragma unroll
         for (int q = 0; q < NKP; q++)
           if (GEN && q < nkin) n_k[a][q] = fs_ld(A->kin[q][a], o1);
       }
     }
-    if (hany) {
+    if (HALO && hany) {
       if (!U0TILE) nh_u0 = fs_ld(hx ? A->u0[0] : A->u0[1], o1h);
-      if (has_force) nh_f = fs_ld(hx ? A->force[0] : A->force[1], o1h);
+      if (GEN && has_force) nh_f = fs_ld(hx ? A->force[0] : A->force[1], o1h);
 #pragma unroll
       for (int q = 0; q < NKP; q++)
         if (GEN && q < nkin) nh_k[q] = fs_ld(hx ? A->kin[q][0] : A->kin[q][1], o1h);
     }
   }
 
-  // k_i and u' of component a from f = convection-diffusion + closure (at most NKP earlier k_j: the host takes the
+  // k_i and u' of one component from f = convection-diffusion + closure (at most NKP earlier k_j: the host takes the
   // exact kernels for longer tableau rows)
-  FS_HD T combine(T f, const int a, const T uc, const T l_u0, const T l_f, const T (&l_k)[NKP], T &f_out) const {
-    (void)a;
-    if (has_force) f = f + l_f;
+  FS_HD T combine(T f, const T uc, const T l_u0, const T l_f, const T (&l_k)[NKP], T &f_out) const {
+    if (GEN && has_force) f = f + l_f;
     f_out = f;
     T acc = U0TILE ? uc : l_u0;
     if (GEN) {
@@ -408,86 +491,89 @@ struct FsThread {
   // is the velocity plane of phase A (q = r + LEAD + 2) part of this block's march?
   FS_HD bool project_active(int r) const { return r + LEAD + 2 <= qlast; }
 
-  // phases A (after the plane's barrier has completed), B, C.  ST: steady state (r >= 0)
-  template <bool ST>
-  FS_HD void pre(const int r) {
+  // phases A (after the plane's barrier has completed), B, C.  ST: steady state (r >= 0).  CELL: this warp owns a row
+  // of cells (compile-time role: the cell warps and the other warps run separate copies of the loop, so that no role
+  // test -- and no register shuffling around a skipped block -- remains inside it).  The halo points ride on the cell
+  // warps 1 / 2 without closure and on the warps 16 / 17 with it.
+  template <bool ST, bool CELL>
+  FS_HD void pre(const int r, const FsOffs<Cfg> &S) {
+    constexpr bool HALO = SMAG ? !CELL : CELL;
     // ---- A: velocity plane r + LEAD is projected in place
-    if (PGRAD && project_active(r))
-      fs_project<T, Cfg>(su + sa * USLOT, su + POFF + sp_a * PSLOT, su + POFF + inc(sp_a, NPS) * PSLOT, tid, K->rh);
-    // ---- B: sigma(r + 2) at this thread's p-cell
+    // (load balance: with the closure the four helper warps 16 .. 19 project, the cell warps have the stencil; without
+    // it the vectors start at warp 3, because warps 1 and 2 carry the halo points)
+    if (PGRAD && !(SMAG && CELL) && project_active(r))
+      fs_project<T, Cfg>(su + S.u_a, su + S.p_a, su + S.p_b, SMAG ? tid - 32 * TY : (tid >= 96 ? tid - 96 : tid + NT - 96),
+                         SMAG ? NT - 32 * TY : NT, K->rh);
+    // ---- B: sigma(r + 2) at this thread's p-cell.  In the steady state the planes beyond the chunk are "computed" as
+    // well (from stale slots, into ring slots nobody reads any more): cheaper than a test around the carried registers
     if (SMAG) {
       const int rB = r + 2;
-      if (sig_thr && (ST || rB >= -3) && rB <= nk) {
-        const int s_mid = add(sq_mid, 2, NS), s_top = add(sq_mid, 3, NS);
-        fs_sigma<T, Cfg, ST>(sg, su + s_mid * USLOT + c_sigu, su + s_top * USLOT + c_sigu, su + SOFF + sg_w * SSLOT + tid, rB, *K);
-      }
+      if ((CELL || sig_thr) && (ST || (rB >= -3 && rB <= nk)))
+        fs_sigma<T, Cfg, ST>(sg, su + S.u_bm + c_sigu, su + S.u_bt + c_sigu, su + S.g_w + c_sigw, rB, *K);
     }
     // ---- C: stencil of plane r
     if (ST || r >= -3) {
-      T *bx = su + DOFF + (r & 1) * Cfg::DXN, *by = su + DOFF + 2 * Cfg::DXN + (r & 1) * Cfg::DYN;
-      const int s_top = inc(sq_mid, NS);
-      const int g_m = SMAG ? add(sg_w, 1, 3) : 0, g_t = SMAG ? add(sg_w, 2, 3) : 0;  // sigma planes r, r+1 (written at r-2, r-1)
-      if (cell_thr) {
+      T *stg = su + S.stg;                                                  // staging rows of this parity: u'_x block ...
+      T *stgy = stg + ((S.stg - DOFF) / Cfg::DXN) * (Cfg::DYN - Cfg::DXN);  // ... and (+ 2 DXN, see d_own_y) the u'_y block
+      if (CELL) {
         T F[3], uc[3], s[3] = {T(0), T(0), T(0)};
-        fs_convdiff<T, Cfg, ST>(cs, su + sq_mid * USLOT + c_own, su + s_top * USLOT + c_own, r, *K, F, uc);
-        if (SMAG && (ST || r >= -2)) fs_divsigma<T, Cfg, ST>(cg, su + SOFF + g_m * SSLOT + c_sig, su + SOFF + g_t * SSLOT + c_sig, r, *K, s);
+        fs_convdiff<T, Cfg, ST>(cs, su + S.u_mid + c_own, su + S.u_top + c_own, r, *K, F, uc);
+        if (SMAG && (ST || r >= -2)) fs_divsigma<T, Cfg, ST>(cg, su + S.g_m + c_sig, su + S.g_t + c_sig, r, *K, s);
         if (ST || r >= 0) {
 #pragma unroll
           for (int a = 0; a < 3; a++) {
             T f;
-            un[a] = combine(F[a] + s[a], a, uc[a], n_u0[a], n_f[a], n_k[a], f);
+            un[a] = combine(F[a] + s[a], uc[a], n_u0[a], n_f[a], n_k[a], f);
             if (has_kout) fs_st(A->kout[a], ob, f);
             fs_st(A->unew[a], ob, un[a]);
           }
-          bx[ty * (TX + 1) + tx + 1] = un[0];
-          by[(ty + 1) * TX + tx] = un[1];
+          stg[d_own_x] = un[0];
+          stgy[d_own_y] = un[1];
         } else if (r == -1 && have_prev) {  // u'_z of the plane below the chunk, for the divergence of its first plane
           T f;
-          cs.uzp = combine(F[2] + s[2], 2, uc[2], n_u0[2], n_f[2], n_k[2], f);
+          cs.uzp = combine(F[2] + s[2], uc[2], n_u0[2], n_f[2], n_k[2], f);
         }
       }
-      if (hany && (ST || r >= -2)) {
+      if (HALO && hany && (ST || r >= -2)) {
         T uc;
-        T F = fs_convdiff_halo<T, Cfg, ST>(hs, ha, su + sq_mid * USLOT + c_halo, su + s_top * USLOT + c_halo, r, *K, uc);
-        if (SMAG) F = F + fs_divsigma_halo<T, Cfg, ST>(hs, ha, su + SOFF + g_m * SSLOT + c_sigh, su + SOFF + g_t * SSLOT + c_sigh, r, *K);
+        T F = fs_convdiff_halo<T, Cfg, ST>(hs, ha, su + S.u_mid + c_halo, su + S.u_top + c_halo, r, *K, uc);
+        if (SMAG) F = F + fs_divsigma_halo<T, Cfg, ST>(hs, ha, su + S.g_m + c_sigh, su + S.g_t + c_sigh, r, *K);
         if (ST || r >= 0) {
           T f;
-          const T v = combine(F, ha, uc, nh_u0, nh_f, nh_k, f);
-          if (hx) bx[hly * (TX + 1)] = v;
-          else by[hlx] = v;
+          const T v = combine(F, uc, nh_u0, nh_f, nh_k, f);
+          (hx ? stg : stgy)[d_halo] = v;
         }
       }
       // operands of plane r + 1 for the next iteration
-      if ((ST || r >= -1) && r + 1 < nk) fetch_operands(plane_off(r + 1) + ocell, plane_off(r + 1) + ohalo);
+      if ((ST || r >= -1) && r + 1 < nk) {
+        const size_t step = (ST || r >= 0) ? szb : 0;  // ob / obh stay on plane 0 until r = 0 (post())
+        fetch_operands<CELL, HALO>(ob + step, obh + step);
+      }
     }
   }
 
-  // after the block barrier: divergence of u' (the neighbours' u'_x, u'_y are in the staging rows), slot advance
-  template <bool ST>
-  FS_HD void post(const int r) {
-    if (cell_thr && (ST || r >= 0)) {
-      const T *bx = su + DOFF + (r & 1) * Cfg::DXN, *by = su + DOFF + 2 * Cfg::DXN + (r & 1) * Cfg::DYN;
+  // after the block barrier: divergence of u' (the neighbours' u'_x, u'_y are in the staging rows)
+  template <bool ST, bool CELL>
+  FS_HD void post(const int r, const FsOffs<Cfg> &S) {
+    if (CELL && (ST || r >= 0)) {
+      const T *stg = su + S.stg;
+      const T *stgy = stg + ((S.stg - DOFF) / Cfg::DXN) * (Cfg::DYN - Cfg::DXN);
       if (r > 0 || have_prev) {
-        T d = (un[0] - bx[ty * (TX + 1) + tx]) * K->rh[0];
-        d += (un[1] - by[ty * TX + tx]) * K->rh[1];
+        T d = (un[0] - stg[d_own_x - 1]) * K->rh[0];
+        d += (un[1] - stgy[d_own_y - TX]) * K->rh[1];
         d += (un[2] - cs.uzp) * K->rh[2];
         fs_st(A->div, ob, d * K->vol);
       }
       cs.uzp = un[2];
     }
     if (ST || r >= 0) { ob += szb; obh += szb; }
-    sq_mid = inc(sq_mid, NS);
-    sa = inc(sa, NS);
-    if (sa == 0) pa_par ^= 1u;
-    sp_a = inc(sp_a, NPS);
-    if (SMAG) sg_w = inc(sg_w, 3);
   }
 };
 
 // ---- the kernel ---------------------------------------------------------------------------------------------------
 #if defined(__CUDACC__)
 template <typename T, bool PGRAD, bool SMAG, bool GEN>
-__global__ void __launch_bounds__(FastCfg<T, SMAG>::NT, ((SMAG || sizeof(T) == 8) ? 1 : 2))
+__global__ void __launch_bounds__(FastCfg<T, SMAG>::NT, ((SMAG || GEN || sizeof(T) == 8) ? 1 : 2))
     k_stage3d_fast(const __grid_constant__ CUtensorMap tm_u, const __grid_constant__ CUtensorMap tm_p,
                    const __grid_constant__ TmaStageArgs<T> A, const __grid_constant__ FastK<T> K, Geo g, int zc, int ox, int oy,
                    int oz) {
@@ -498,9 +584,10 @@ __global__ void __launch_bounds__(FastCfg<T, SMAG>::NT, ((SMAG || sizeof(T) == 8
   T *su = reinterpret_cast<T *>(sb);
   uint64_t *bars = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(su + Cfg::ELEMS) + 7) & ~(uintptr_t)7);
   const int tid = threadIdx.y * Cfg::TX + threadIdx.x;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);  // warp-uniform by construction: role tests become uniform branches
 
   FsThread<T, PGRAD, SMAG, GEN> t;
-  t.init(su, &A, &K, g, zc, tid, blockIdx.x, blockIdx.y, blockIdx.z);
+  t.init(su, &A, &K, g, zc, tid, warp, blockIdx.x, blockIdx.y, blockIdx.z);
 
   // velocity plane q <-> z = kbeg - 2 + q; q = 0 .. qlast are loaded, NS slots, one mbarrier per slot
   const int x0 = ox + blockIdx.x * Cfg::TX - Cfg::XL, y0 = oy + blockIdx.y * Cfg::TY - 2, z0 = oz + t.kbeg - 2;
@@ -522,28 +609,62 @@ __global__ void __launch_bounds__(FastCfg<T, SMAG>::NT, ((SMAG || sizeof(T) == 8
     }
     tma_load_4d(su + (q % NS) * Cfg::USLOT, &tm_u, bar, x0, y0, z0 + q, 0);
   };
-  if (tid == 0) {
+  if (tid == 0) {  // NS - 1 planes: the pressure ring holds planes 0 .. NS-1 at this point
 #pragma unroll
-    for (int q = 0; q < NS; q++)
+    for (int q = 0; q < NS - 1; q++)
       if (q <= t.qlast) issue(q);
   }
-  int r = Cfg::R0;
-  for (; r < 0; r++) {  // start-up: the pipeline fills, carried values are set up (general code, a few iterations)
-    if (t.project_active(r)) mbar_wait(&bars[t.sa], t.pa_par);  // plane r + LEAD has landed
-    t.template pre<false>(r);
-    __syncthreads();
-    // velocity plane r (q = r + 2) is retired: its slot takes plane q + NS
-    if (tid == 0 && r >= -2 && r + 2 + NS <= t.qlast) issue(r + 2 + NS);
-    t.template post<false>(r);
-  }
-#pragma unroll 2
-  for (; r < t.nk; r++) {  // steady state
-    if (t.project_active(r)) mbar_wait(&bars[t.sa], t.pa_par);
-    t.template pre<true>(r);
-    __syncthreads();
-    if (tid == 0 && r + 2 + NS <= t.qlast) issue(r + 2 + NS);
-    t.template post<true>(r);
-  }
+  // One iteration: wait for plane r + LEAD, phases A / B / C, block barrier, refill (thread 0), divergence.  After the
+  // barrier velocity plane r (q = r + 2) is retired and its slot takes plane q + NS (the very first iteration frees
+  // pressure slot 0 instead, which plane NS - 1 was waiting for).  The cell warps and the other warps (closure only:
+  // sigma tile, halo points) run their own copy of the loop and meet at the same hardware barrier.
+  auto march = [&](auto cellc) {
+    constexpr bool CELL = decltype(cellc)::value != 0;
+    auto barrier_of = [&](int r) -> uint64_t * { return &bars[(r + Cfg::LEAD + 2) & (NS - 1)]; };
+    auto parity_of = [&](int r) -> uint32_t { return (uint32_t)(((r + Cfg::LEAD + 2) >> 3) & 1); };
+    int r = Cfg::R0;
+    for (; r < 0; r++) {  // start-up: the pipeline fills, carried values are set up (general code, a few iterations)
+      const FsOffs<Cfg> S = FsOffs<Cfg>::make(r);
+      if (t.project_active(r)) mbar_wait(barrier_of(r), parity_of(r));  // plane r + LEAD has landed
+      t.template pre<false, CELL>(r, S);
+      asm volatile("bar.sync 0;" ::: "memory");
+      if (CELL && tid == 0) {
+        if (r == Cfg::R0 && NS - 1 <= t.qlast) issue(NS - 1);
+        if (r >= -2 && r + 2 + NS <= t.qlast) issue(r + 2 + NS);
+      }
+      t.template post<false, CELL>(r, S);
+    }
+    // steady state, 4 planes per trip: r = 4 g + J, all shared-memory offsets are immediates +- H (FsOffs::steady)
+    int H = 0, HP = 0;
+    auto one = [&](auto jc) {
+      constexpr int J = decltype(jc)::value;
+      const FsOffs<Cfg> S = FsOffs<Cfg>::template steady<J>(H, HP);
+      if (t.project_active(r)) mbar_wait(barrier_of(r), parity_of(r));
+      t.template pre<true, CELL>(r, S);
+      asm volatile("bar.sync 0;" ::: "memory");
+      if (CELL && tid == 0 && r + 2 + NS <= t.qlast) issue(r + 2 + NS);
+      t.template post<true, CELL>(r, S);
+      r++;
+    };
+    for (; r + 4 <= t.nk;) {
+      one(IntC<0>{});
+      one(IntC<1>{});
+      one(IntC<2>{});
+      one(IntC<3>{});
+      H = 4 * Cfg::USLOT - H;
+      HP = 4 * Cfg::PSLOT - HP;
+    }
+    for (; r < t.nk; r++) {  // tail (fewer than 4 planes left): general offsets
+      const FsOffs<Cfg> S = FsOffs<Cfg>::make(r);
+      if (t.project_active(r)) mbar_wait(barrier_of(r), parity_of(r));
+      t.template pre<true, CELL>(r, S);
+      asm volatile("bar.sync 0;" ::: "memory");
+      if (CELL && tid == 0 && r + 2 + NS <= t.qlast) issue(r + 2 + NS);
+      t.template post<true, CELL>(r, S);
+    }
+  };
+  if (!SMAG || warp < Cfg::TY) march(IntC<1>{});
+  else march(IntC<0>{});
 }
 #endif  // __CUDACC__
 

@@ -1697,7 +1697,8 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
     int nkrow = 0;  // earlier stage derivatives this tableau row reads
     for (int j = 0; j < i; j++) nkrow += tb.A[i * tb.s + j] != 0.0;
     // fused closure + stage kernel (fast.cu) for rows with at most 3 earlier k_j; `exact` and longer rows keep the two kernels below
-    const bool fast = stage_fast_supported(c, smag) && nkrow <= 3;
+    const bool gen_row = nkrow > 0 || !tb.need[i] || c->force;
+    const bool fast = stage_fast_supported(c, smag) && nkrow <= 3 && (smag || !gen_row || c->fast_gen);
     if (smag && !fast) {
       INS_TRY(ensure_vec(c, &c->sbuf));
       INS_TRY((launch_smag_tma<T>(c, theta, c->ubuf[cur], pbase)));
@@ -2117,6 +2118,7 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   clear_graphs(c);  // a captured step holds the launch configuration of the parameters it was captured with
   if (k == "variant") c->variant = v;
   else if (k == "exact") c->exact = v != 0;   // 1: bit-exact kernels (reference operation order, no contraction); 0: fast kernels (fast.cu)
+  else if (k == "fast_gen") c->fast_gen = v != 0;
   else if (k == "graphs") c->use_graphs = v;  // 1 on, 0 off, -1 automatic (small grids)
   else if (k == "tile_y") { if (v != 8 && v != 16) INS_FAIL(c, "tile_y must be 8 or 16"); c->tile_y = v; }
   else if (k == "zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "zchunk must be 0 (automatic) or >= 2"); c->zchunk = v; }

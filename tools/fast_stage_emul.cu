@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <random>
 #include <vector>
 
@@ -48,6 +49,12 @@ struct Ref {  // periodic interior arrays in double, index (c, k, j, i)
     return ((size_t)c * n2 + Padded::wrap(k, n2)) * n1 * n0 + (size_t)Padded::wrap(j, n1) * n0 + Padded::wrap(i, n0);
   }
 };
+
+template <typename O>
+static bool same_offs(const O &a, const O &b) {
+  return a.u_mid == b.u_mid && a.u_top == b.u_top && a.u_bm == b.u_bm && a.u_bt == b.u_bt && a.u_a == b.u_a && a.p_a == b.p_a &&
+         a.p_b == b.p_b && a.g_w == b.g_w && a.g_m == b.g_m && a.g_t == b.g_t && a.stg == b.stg;
+}
 
 template <bool PGRAD, bool SMAG, bool GEN>
 static int run_variant(int n0, int n1, int n2, int zc, bool force, int nkin, bool kout) {
@@ -171,7 +178,7 @@ static int run_variant(int n0, int n1, int n2, int zc, bool force, int nkin, boo
     for (int by = 0; by < n1 / Cfg::TY; by++)
       for (int bx = 0; bx < n0 / Cfg::TX; bx++) {
         for (auto &v : smem) v = std::nanf("");  // anything read before it is written shows up
-        for (int t = 0; t < Cfg::NT; t++) th[t].init(smem.data(), &A, &K, g, zc, t, bx, by, bz);
+        for (int t = 0; t < Cfg::NT; t++) th[t].init(smem.data(), &A, &K, g, zc, t, t >> 5, bx, by, bz);
         const int kbeg = th[0].kbeg, nk = th[0].nk, qlast = th[0].qlast;
         const int x0 = P.org[0] + bx * Cfg::TX - Cfg::XL, y0 = P.org[1] + by * Cfg::TY - 2, z0 = P.org[2] + kbeg - 2;
         auto box = [&](T *dst, const std::vector<T> &src, int nc, int rows, int z) {  // cp.async.bulk.tensor.4d, box (BX, rows, 1, nc)
@@ -189,17 +196,36 @@ static int run_variant(int n0, int n1, int n2, int zc, bool force, int nkin, boo
           }
           box(smem.data() + (q % Cfg::NS) * Cfg::USLOT, d_up, 3, Cfg::BY, z0 + q);
         };
-        for (int q = 0; q < Cfg::NS; q++) if (q <= qlast) issue(q);
+        for (int q = 0; q < Cfg::NS - 1; q++) if (q <= qlast) issue(q);
         int r = Cfg::R0;
         for (; r < 0; r++) {
-          for (int t = 0; t < Cfg::NT; t++) th[t].template pre<false>(r);
+          const FsOffs<Cfg> S = FsOffs<Cfg>::make(r);
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template pre<false, true>(r, S); else th[t].template pre<false, false>(r, S); }
+          if (r == Cfg::R0 && Cfg::NS - 1 <= qlast) issue(Cfg::NS - 1);
           if (r >= -2 && r + 2 + Cfg::NS <= qlast) issue(r + 2 + Cfg::NS);
-          for (int t = 0; t < Cfg::NT; t++) th[t].template post<false>(r);
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template post<false, true>(r, S); else th[t].template post<false, false>(r, S); }
+        }
+        int H = 0, HP = 0;
+        auto one = [&](auto jc) {
+          constexpr int J = decltype(jc)::value;
+          const FsOffs<Cfg> S = FsOffs<Cfg>::template steady<J>(H, HP);
+          const FsOffs<Cfg> G = FsOffs<Cfg>::make(r);  // the unrolled offsets must equal the general ones
+          if (!same_offs(S, G)) { printf("steady offsets differ at r = %d\n", r); exit(3); }
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template pre<true, true>(r, S); else th[t].template pre<true, false>(r, S); }
+          if (r + 2 + Cfg::NS <= qlast) issue(r + 2 + Cfg::NS);
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template post<true, true>(r, S); else th[t].template post<true, false>(r, S); }
+          r++;
+        };
+        for (; r + 4 <= nk;) {
+          one(IntC<0>{}); one(IntC<1>{}); one(IntC<2>{}); one(IntC<3>{});
+          H = 4 * Cfg::USLOT - H;
+          HP = 4 * Cfg::PSLOT - HP;
         }
         for (; r < nk; r++) {
-          for (int t = 0; t < Cfg::NT; t++) th[t].template pre<true>(r);
+          const FsOffs<Cfg> S = FsOffs<Cfg>::make(r);
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template pre<true, true>(r, S); else th[t].template pre<true, false>(r, S); }
           if (r + 2 + Cfg::NS <= qlast) issue(r + 2 + Cfg::NS);
-          for (int t = 0; t < Cfg::NT; t++) th[t].template post<true>(r);
+          for (int t = 0; t < Cfg::NT; t++) { if (th[t].cell_thr) th[t].template post<true, true>(r, S); else th[t].template post<true, false>(r, S); }
         }
       }
 
@@ -231,10 +257,12 @@ int main(int argc, char **argv) {
   printf("fast_stage_emul: grid %d x %d x %d, z-chunks of %d planes\n", n0, n1, n2, zc);
   int fails = 0;
   fails += run_variant<false, false, false>(n0, n1, n2, zc, false, 0, true);   // first stage
-  fails += run_variant<true, false, false>(n0, n1, n2, zc, true, 0, true);     // middle stage + force
+  fails += run_variant<true, false, false>(n0, n1, n2, zc, false, 0, true);    // middle stage
+  fails += run_variant<true, false, true>(n0, n1, n2, zc, true, 0, true);      // middle stage + force (GEN kernel)
   fails += run_variant<true, false, true>(n0, n1, n2, zc, false, 3, false);    // last RK44 row
   fails += run_variant<false, true, false>(n0, n1, n2, zc, false, 0, true);    // closure, first stage
-  fails += run_variant<true, true, false>(n0, n1, n2, zc, true, 0, true);      // closure, middle stage + force
+  fails += run_variant<true, true, false>(n0, n1, n2, zc, false, 0, true);     // closure, middle stage
+  fails += run_variant<true, true, true>(n0, n1, n2, zc, true, 0, true);       // closure, middle stage + force (GEN kernel)
   fails += run_variant<true, true, true>(n0, n1, n2, zc, false, 2, true);      // closure, general row with 2 earlier k_j
   printf(fails ? "FAILED (%d)\n" : "all variants agree\n", fails);
   return fails != 0;
