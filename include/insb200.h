@@ -63,6 +63,13 @@ int insb200_synchronize(insb200_ctx *ctx);
 /* Local slab geometry: nloc[D] interior cells of this rank, offset of its first plane on the last axis. */
 int insb200_local_geometry(const insb200_ctx *ctx, int *nloc, int *last_axis_offset);
 
+/* The slab decomposition itself, as pure host arithmetic (no device, no ctx; insb200_create uses the same function):
+ * rank owns the planes [z0, z0 + nzl) of the last axis (n_last cells) and, in the transposed spectrum of the
+ * distributed pressure solve, the wavenumbers kx in [kx0, kx0 + kxl) of the halved first axis (n_first / 2 + 1 values:
+ * n_first / 2 + 1 over nranks columns per rank, the last rank also takes the remainder).  The reference is
+ * single-device; this is the contract the multi-GPU tests pin.  Returns 0, or 1 on bad arguments. */
+int insb200_decomposition(int n_first, int n_last, int rank, int nranks, int *z0, int *nzl, int *kx0, int *kxl);
+
 /* ---- operators on device fields (reference layout) ----------------------------------------- */
 
 /* apply_bc_u!(u, t, setup), PeriodicBC: src/boundary_conditions.jl:159-167, 276-288 */

@@ -7,7 +7,7 @@ libinsb200.so), `_lib.py` (ctypes prototypes), `api.py` / `processors.py` / `ini
 """
 from . import _lib  # noqa: F401
 from .api import *  # noqa: F401,F403
-from .api import Observable, ExplicitRungeKuttaMethod, get_state, slab_bounds  # noqa: F401
+from .api import Observable, ExplicitRungeKuttaMethod, decomposition, get_state, slab_bounds  # noqa: F401
 from .initializers import create_spectrum, random_field, velocityfield  # noqa: F401
 from .processors import checkpointer, load_checkpoint, save_checkpoint  # noqa: F401
 from .processors import energy_history, fieldsaver, observefield, observespectrum, processor, spectral_stuff, timelogger  # noqa: F401

@@ -23,6 +23,7 @@ PROTOTYPES = {
     "insb200_set_stream": (c_int, [c_void_p, c_void_p]),
     "insb200_synchronize": (c_int, [c_void_p]),
     "insb200_local_geometry": (c_int, [c_void_p, P(c_int), P(c_int)]),
+    "insb200_decomposition": (c_int, [c_int, c_int, c_int, c_int, P(c_int), P(c_int), P(c_int), P(c_int)]),
     "insb200_apply_bc_u": (c_int, [c_void_p, c_void_p]),
     "insb200_apply_bc_p": (c_int, [c_void_p, c_void_p]),
     "insb200_set_bodyforce": (c_int, [c_void_p, c_void_p]),

@@ -895,12 +895,20 @@ class Observable:
 # --------------------------------------------------------------------------------------------
 # slab helpers (host side of the multi-GPU decomposition: SURVEY 8e)
 # --------------------------------------------------------------------------------------------
+def decomposition(n_first, n_last, rank, nranks):
+    """(z0, nzl, kx0, kxl) of `rank`: its planes of the last axis and its kx range of the transposed spectrum of the
+    distributed pressure solve -- `insb200_decomposition`, the host arithmetic `insb200_create` itself uses."""
+    lib = _lib.load()
+    z0, nzl, kx0, kxl = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    if lib.insb200_decomposition(int(n_first), int(n_last), int(rank), int(nranks), C.byref(z0), C.byref(nzl), C.byref(kx0), C.byref(kxl)):
+        raise ValueError("the last axis must be divisible by the number of ranks")
+    return z0.value, nzl.value, kx0.value, kxl.value
+
+
 def slab_bounds(n_last, rank, nranks):
     """[first, last) interior planes of the last axis owned by `rank`."""
-    if n_last % nranks:
-        raise ValueError("the last axis must be divisible by the number of ranks")
-    m = n_last // nranks
-    return rank * m, (rank + 1) * m
+    z0, nzl, _, _ = decomposition(2, n_last, rank, nranks)
+    return z0, z0 + nzl
 
 
 def local_slab(a_global, D, rank, nranks):

@@ -53,13 +53,13 @@ struct Geo {
 enum TimerId {
   TM_IMPORT = 0, TM_EXPORT, TM_BC, TM_MOMENTUM, TM_STAGE, TM_SMAGTENSOR, TM_DIVTENSOR, TM_DIVERGENCE,
   TM_FFT_FWD, TM_FFT_INV, TM_POISSON_SCALE, TM_GRADIENT, TM_REDUCE, TM_HALO, TM_PACK, TM_A2A,
-  TM_MISC, TM_STAGE_GEN, TM_SMAG_FUSED, TM_GHOSTS, TM_COUNT
+  TM_MISC, TM_STAGE_GEN, TM_SMAG_FUSED, TM_GHOSTS, TM_SCATTER, TM_COUNT
 };
 static const char *const kTimerNames[TM_COUNT] = {
     "import_ghosted", "export_ghosted", "apply_bc", "momentum", "momentum_stage", "smagtensor",
     "divoftensor", "divergence", "cufft_forward", "cufft_inverse", "poisson_scale", "pressure_gradient",
     "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc", "momentum_stage_last", "smagorinsky_fused",
-    "fill_ghosts"};
+    "fill_ghosts", "fft_transpose"};
 
 struct TimerRec {
   cudaEvent_t a, b;
@@ -143,7 +143,10 @@ struct insb200_ctx {
   int nxp = 0;                                          // row pitch (complex words) of the in-slab spectrum, >= nxh
   int p2p = 0;                                          // 1: peer mappings established, transposes go over peer stores
   int p2p_enable = 1;                                   // param "p2p": 0 forces the NCCL send/recv transpose
-  void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter
+  void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter (NCCL fallback)
+  void *flagbuf = nullptr, *peerF[16] = {nullptr};      // barrier flag words of this rank / of every rank (CUDA IPC): k_peer_barrier
+  unsigned bar_epoch = 0;                               // barriers issued so far (same sequence on every rank)
+  int fast_barrier = 1;                                 // param "fast_barrier": 0 = ncclAllReduce barriers
   void *ztw = nullptr;                                  // twiddles exp(-2 pi i t / n_last) of k_zsolve (complex T)
   void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)
   void *hostio = nullptr;                               // reference-layout device image for *_host calls
@@ -234,15 +237,16 @@ struct ScopedTimer {
   insb200_ctx *c;
   int id;
   cudaEvent_t a = nullptr, b = nullptr;
-  ScopedTimer(insb200_ctx *c_, int id_) : c(c_), id(id_) {
+  cudaStream_t st;
+  ScopedTimer(insb200_ctx *c_, int id_, cudaStream_t st_ = nullptr) : c(c_), id(id_), st(st_ ? st_ : c_->stream) {
     if (!c->profiling) return;
     a = take();
     b = take();
-    cudaEventRecord(a, c->stream);
+    cudaEventRecord(a, st);
   }
   ~ScopedTimer() {
     if (!c->profiling) return;
-    cudaEventRecord(b, c->stream);
+    cudaEventRecord(b, st);
     c->recs.push_back({a, b, id});
   }
   cudaEvent_t take() {

@@ -14,6 +14,7 @@
 #include "tma_stage_x2.cuh"
 #include "stage2d.cuh"
 #include "zsolve.cuh"
+#include "comm.cuh"
 #include "fast.cuh"
 
 namespace insb200 {
@@ -113,6 +114,23 @@ static double sinpi01(double x) {  // x in [0,1]; reduced so that multiples of 1
   if (!(c)) return 1; \
   if (cudaSetDevice((c)->device) != cudaSuccess) INS_FAIL((c), "cudaSetDevice failed")
 
+// ---- barrier over peer memory -------------------------------------------------------------------------
+// "every rank's peer stores issued so far on its stream are complete and visible to what follows on mine".  With the
+// flag buffers mapped (setup_p2p) this is the 32-thread kernel k_peer_barrier (comm.cuh); otherwise -- and with
+// set_param("fast_barrier", 0) -- a 4-byte ncclAllReduce.  All barriers of a context go to c->stream, in the same
+// order on every rank, so one epoch counter serves them all.
+static int peer_barrier(insb200_ctx *c) {
+  if (c->fast_barrier && c->peerF[0]) {
+    PeerPtrs F;
+    for (int q = 0; q < 16; q++) F.p[q] = c->peerF[q];
+    k_peer_barrier<<<1, 32, 0, c->stream>>>(F, c->rank, c->nranks, ++c->bar_epoch, 0);
+    CHECK_LAUNCH(c);
+    return 0;
+  }
+  INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
+  return 0;
+}
+
 // ---- halo exchange along the decomposed axis (nranks > 1) ---------------------------------------
 // compact buffer with c->G ghost planes each side; ncomp components of stride ccomp.
 // wminus planes: my bottom ghosts <- prev's top interior planes; wplus: my top ghosts <- next's bottom.
@@ -127,19 +145,13 @@ static int halo_compact(insb200_ctx *c, void *base, int ncomp, int wminus, int w
   if (wminus > G || wplus > Gp || wminus > nl || wplus > nl) INS_FAIL(c, "halo width exceeds the ghost planes");
   auto hp = c->halo_peers.find(base);
   if (c->p2p && c->p2p_halo && hp != c->halo_peers.end()) {
-    // registered buffer: the planes go straight into the ring neighbours' ghost planes (copy engines over NVLink,
-    // buffers mapped with CUDA IPC); the 4-byte all-reduce orders them before the consumers on every rank
-    for (int q = 0; q < ncomp; q++) {
-      const i64 co = q * c->ccomp;
-      if (wminus > 0)
-        INS_CUDA(c, cudaMemcpyAsync((T *)hp->second.next + co + (G - wminus) * pl, (T *)base + co + (G + nl - wminus) * pl,
-                                    (size_t)(wminus * pl) * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
-      if (wplus > 0)
-        INS_CUDA(c, cudaMemcpyAsync((T *)hp->second.prev + co + (G + nl) * pl, (T *)base + co + G * pl,
-                                    (size_t)(wplus * pl) * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
-    }
-    INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
-    return 0;
+    // registered buffer: ONE kernel stores all planes of all components straight into the ring neighbours' ghost
+    // planes (buffers mapped with CUDA IPC), the flag barrier orders them before the consumers on every rank
+    const i64 nmax = (i64)std::max(wminus, wplus) * pl;
+    dim3 grd((unsigned)std::min<i64>((nmax / (16 / sizeof(T)) + 255) / 256, 4 * (i64)c->nsm), ncomp, 2);
+    k_halo_push<T><<<grd, 256, 0, c->stream>>>((T *)hp->second.next, (T *)hp->second.prev, (const T *)base, c->ccomp, pl, nl, (int)G, wminus, wplus);
+    CHECK_LAUNCH(c);
+    return peer_barrier(c);
   }
   INS_NCCL(c, ncclGroupStart());
   for (int q = 0; q < ncomp; q++) {
@@ -197,6 +209,16 @@ static int upload_symbol(insb200_ctx *c) {
   return 0;
 }
 
+extern "C" int insb200_decomposition(int n_first, int n_last, int rank, int nranks, int *z0, int *nzl, int *kx0, int *kxl) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || n_first < 2 || n_last < 1 || n_last % nranks) return 1;
+  const int nxh = n_first / 2 + 1, kxc = nxh / nranks;
+  if (nzl) *nzl = n_last / nranks;
+  if (z0) *z0 = rank * (n_last / nranks);
+  if (kx0) *kx0 = rank * kxc;
+  if (kxl) *kxl = rank == nranks - 1 ? nxh - rank * kxc : kxc;
+  return 0;
+}
+
 extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype, const double *h, double Re,
                               int device, int rank, int nranks, const void *nccl_id) {
   if (!out) { g_create_error = "ctx output pointer is NULL"; return 1; }
@@ -221,8 +243,10 @@ extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype,
   c->D = D; c->dtype = dtype; c->Re = Re; c->device = device; c->rank = rank; c->nranks = nranks;
   c->last = D - 1;
   for (int a = 0; a < D; a++) { c->nglob[a] = n[a]; c->nloc[a] = n[a]; c->h[a] = h[a]; }
-  c->nloc[c->last] = n[c->last] / nranks;
-  c->off_last = rank * c->nloc[c->last];
+  if (insb200_decomposition(n[0], n[c->last], rank, nranks, &c->off_last, &c->nloc[c->last], &c->kx0, &c->kxl)) {
+    delete c;
+    INS_FAIL(nullptr, "bad decomposition");
+  }
   if (D == 3) {
     // padded layout (ctx.cuh): 64 B of x margin each side, gm/gp ghost layers in y and z
     const int es = dtype == INSB200_F64 ? 8 : 4;
@@ -247,11 +271,10 @@ extern "C" int insb200_create(insb200_ctx **out, int D, const int *n, int dtype,
     c->corg = (i64)c->G * c->cplane;
   }
   c->nxh = n[0] / 2 + 1;
-  c->kxc = (c->nxh + nranks - 1) / nranks;
-  if (nranks > 1 && dtype == INSB200_F32) c->kxc = (c->kxc + 1) & ~1;  // 16-B aligned chunk starts (TMA on the peers' spectra)
+  // kx split of the transposed spectrum: nxh / nranks columns per rank, the LAST rank also takes the remainder
+  // (n = 1024 on 8 ranks: 64 columns = 512-byte rows each, the last rank 65 with the Nyquist column)
+  c->kxc = c->nxh / nranks;  // kx0, kxl: insb200_decomposition above
   c->nxp = c->nxh;
-  c->kx0 = std::min(rank * c->kxc, c->nxh);
-  c->kxl = std::min((rank + 1) * c->kxc, c->nxh) - c->kx0;
 
   auto bail = [&](int r) { std::string e = c->err; insb200_destroy(c); g_create_error = e; return r; };
   if (cudaSetDevice(device) != cudaSuccess) { c->err = "cudaSetDevice failed"; return bail(1); }
@@ -356,8 +379,9 @@ static void close_p2p(insb200_ctx *c) {
     if (q != c->rank) {
       if (c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
       if (c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
+      if (c->peerF[q]) cudaIpcCloseMemHandle(c->peerF[q]);
     }
-    c->peerS[q] = c->peerB[q] = nullptr;
+    c->peerS[q] = c->peerB[q] = c->peerF[q] = nullptr;
   }
   c->p2p = 0;
 }
@@ -368,14 +392,17 @@ static void close_p2p(insb200_ctx *c) {
 static int setup_p2p(insb200_ctx *c) {
   if (!c->p2p_enable || c->nranks > 16) return 0;
   struct Rec {
-    cudaIpcMemHandle_t h[2];
+    cudaIpcMemHandle_t h[3];
     int ok, pad[15];
   };
   INS_TRY(dev_alloc(c, &c->barbuf, 256));
+  INS_TRY(dev_alloc(c, &c->flagbuf, (size_t)2 << 20));  // zeroed: epochs start at 1.  2 MiB: an allocation of its own (IPC maps whole allocations)
+  INS_CUDA(c, cudaStreamSynchronize(c->stream));
   std::vector<Rec> all(c->nranks);
   Rec mine;
   memset(&mine, 0, sizeof(mine));
-  mine.ok = cudaIpcGetMemHandle(&mine.h[0], c->pcplx) == cudaSuccess && cudaIpcGetMemHandle(&mine.h[1], c->pcplx2) == cudaSuccess;
+  mine.ok = cudaIpcGetMemHandle(&mine.h[0], c->pcplx) == cudaSuccess && cudaIpcGetMemHandle(&mine.h[1], c->pcplx2) == cudaSuccess &&
+            cudaIpcGetMemHandle(&mine.h[2], c->flagbuf) == cudaSuccess;
   if (!mine.ok) cudaGetLastError();
   void *dev = nullptr;
   INS_CUDA(c, cudaMalloc(&dev, sizeof(Rec) * c->nranks));
@@ -387,9 +414,10 @@ static int setup_p2p(insb200_ctx *c) {
   for (int q = 0; q < c->nranks; q++) ok &= all[q].ok;
   if (ok) {
     for (int q = 0; q < c->nranks && ok; q++) {
-      if (q == c->rank) { c->peerS[q] = c->pcplx; c->peerB[q] = c->pcplx2; continue; }
+      if (q == c->rank) { c->peerS[q] = c->pcplx; c->peerB[q] = c->pcplx2; c->peerF[q] = c->flagbuf; continue; }
       if (cudaIpcOpenMemHandle(&c->peerS[q], all[q].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerS[q] = nullptr; ok = 0; }
       else if (cudaIpcOpenMemHandle(&c->peerB[q], all[q].h[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerB[q] = nullptr; ok = 0; }
+      else if (cudaIpcOpenMemHandle(&c->peerF[q], all[q].h[2], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerF[q] = nullptr; ok = 0; }
     }
     if (!ok) cudaGetLastError();
   }
@@ -493,7 +521,8 @@ static int ensure_fft(insb200_ctx *c) {
     const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
     // row pitch of the in-slab spectrum: a multiple of 16 B so that the peers can address it by TMA
     if (D == 3 && f32) c->nxp = (c->nxh + 1) & ~1;
-    const i64 slots = std::max((i64)c->nranks * c->kxc, (i64)c->nxp) * rows;  // >= rows*nxp and >= nranks*rows*kxl
+    const i64 kxmax = c->nxh - (i64)(c->nranks - 1) * c->kxc;                 // the last rank's (largest) column count
+    const i64 slots = std::max((i64)c->nranks * kxmax, (i64)c->nxp) * rows;   // >= rows*nxp and >= nranks*rows*kxl
     INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
     INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
     if (D == 3) {
@@ -759,6 +788,7 @@ static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T
   return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
 }
 
+#ifdef INSB200_EXPERIMENTAL
 // fused transposes + last-axis solve over the peers' in-slab spectra (k_zsolve_peer)
 template <typename T, int COLS>
 static int launch_zsolve_peer_i(insb200_ctx *c, T invN, const ZRadix &rad, bool local_load) {
@@ -826,6 +856,8 @@ static int launch_zsolve_peer(insb200_ctx *c, T invN, bool local_load) {
   return launch_zsolve_peer_i<T, 4>(c, invN, rad, local_load);
 }
 
+#endif  // INSB200_EXPERIMENTAL
+
 // ---- spectral Poisson solve on the compact real buffer (in: preal interior = rhs; out: solution) --
 template <typename T, int D>
 static int poisson_solve(insb200_ctx *c) {
@@ -863,20 +895,17 @@ static int poisson_solve(insb200_ctx *c) {
     }
     return 0;
   }
-  // ---- slab-decomposed transform: in-slab FFT -> pack -> all-to-all -> last-axis FFT -> scale -> back
+  // ---- slab-decomposed transform: in-slab FFT -> transpose -> last-axis solve -> transpose back -> in-slab inverse FFT
   C *B = (C *)c->pcplx2;
+  const int P = c->nranks;
   const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
   const ncclDataType_t dt = sizeof(T) == 4 ? ncclFloat : ncclDouble;
-  auto chunk_w = [&](int q) { return std::max(0, std::min((q + 1) * c->kxc, c->nxh) - q * c->kxc); };
+  auto chunk_w = [&](int q) { return q == P - 1 ? c->nxh - q * c->kxc : c->kxc; };
   dim3 pblk(64, 4, 1), pgrd((unsigned)((rows + 3) / 4), (c->nxh + 63) / 64, 1);
-  dim3 sgrd((unsigned)((rows + 4 * kScatterRows - 1) / (4 * kScatterRows)), c->nranks, 1);  // scatter kernels: y = destination
-  const bool pipelined = c->p2p && !c->p2p_fused && D == 3 && zsolve_supported(c) && c->fft_pipe > 1 && c->fft_batch * c->fft_pipe == c->nloc[2];
-  if (!pipelined) INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
+  dim3 sblk(32, kSc2Warps, 1);
+  auto sgrid = [&](i64 nr) { return dim3((unsigned)((nr + kSc2Warps * kSc2Rows - 1) / (kSc2Warps * kSc2Rows)), P, 1); };
+  const bool pipelined = c->p2p && D == 3 && zsolve_supported(c) && c->fft_pipe > 1 && c->fft_batch * c->fft_pipe == c->nloc[2];
   C *W = c->p2p ? B : S;  // the transposed spectrum (kxl fastest, ky, global z) of this rank
-  auto peer_barrier = [&]() -> int {  // all ranks' peer stores issued so far are complete and visible afterwards
-    INS_NCCL(c, ncclAllReduce(c->barbuf, c->barbuf, 1, ncclInt, ncclMax, c->comm, c->stream));
-    return 0;
-  };
   PeerPtrs pS, pB;
   for (int q = 0; q < 16; q++) { pS.p[q] = c->peerS[q]; pB.p[q] = c->peerB[q]; }
   if (pipelined) {
@@ -889,7 +918,6 @@ static int poisson_solve(insb200_ctx *c) {
       for (int b = 0; b < 16; b++) INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_ev[b], cudaEventDisableTiming));
       INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_sync, cudaEventDisableTiming));
     }
-    dim3 sg((unsigned)((rb + 4 * kScatterRows - 1) / (4 * kScatterRows)), c->nranks, 1);
     {
       ScopedTimer tm(c, TM_FFT_FWD);
       for (int b = 0; b < NB; b++) {
@@ -899,7 +927,8 @@ static int poisson_solve(insb200_ctx *c) {
         else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)r, (cufftDoubleComplex *)s));
         INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->stream));
         INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_ev[b], 0));
-        k_fft_scatter_fwd<C><<<sg, pblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, 0, b * rb, (b + 1) * rb);
+        ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
+        k_fft_scatter2_fwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, b * rb, (b + 1) * rb);
         CHECK_LAUNCH(c);
       }
       c->fft_execs++;
@@ -908,14 +937,15 @@ static int poisson_solve(insb200_ctx *c) {
       ScopedTimer tm(c, TM_A2A);
       INS_CUDA(c, cudaEventRecord(c->pipe_sync, c->comm_stream));
       INS_CUDA(c, cudaStreamWaitEvent(c->stream, c->pipe_sync, 0));
-      INS_TRY(peer_barrier());
+      INS_TRY(peer_barrier(c));
     }
     if (c->kxl > 0) INS_TRY((launch_zsolve<T>(c, B, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
     INS_CUDA(c, cudaEventRecord(c->pipe_sync, c->stream));
     INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_sync, 0));
     for (int b = 0; b < NB; b++) {
       if (c->kxl > 0) {
-        k_fft_scatter_bwd<C><<<sg, pblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, c->nranks, b * rb, (b + 1) * rb);
+        ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
+        k_fft_scatter2_bwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, P, b * rb, (b + 1) * rb);
         CHECK_LAUNCH(c);
       }
       INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->comm_stream));
@@ -924,7 +954,7 @@ static int poisson_solve(insb200_ctx *c) {
       ScopedTimer tm(c, TM_FFT_INV);
       for (int b = 0; b < NB; b++) {
         INS_CUDA(c, cudaStreamWaitEvent(c->stream, c->pipe_ev[b], 0));
-        INS_TRY(peer_barrier());  // chunk b of every rank's spectrum is complete
+        INS_TRY(peer_barrier(c));  // chunk b of every rank's spectrum is complete
         T *r = pr + (i64)b * c->fft_batch * c->csz;
         C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
         if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)s, (cufftReal *)r));
@@ -934,38 +964,25 @@ static int poisson_solve(insb200_ctx *c) {
     }
     return 0;
   }
-  if (c->p2p && c->p2p_fused && D == 3 && zsolve_supported(c) && c->nranks <= 8) {
-    // p2p_fused = 2: every rank gathers its kx range of the peers' spectra inside the solve kernel (peer loads);
-    // p2p_fused = 1: the way there is k_fft_scatter_fwd (peer stores), only the way back is fused into the solve
-    const bool local_load = c->p2p_fused == 1;
-    if (local_load) {
-      ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_fwd<C><<<sgrd, pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, sizeof(T) == 4, 0, rows);
-      CHECK_LAUNCH(c);
-    }
-    { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all in-slab transforms / forward scatters are complete
-    if (c->kxl > 0) INS_TRY((launch_zsolve_peer<T>(c, invN, local_load)));
-    { ScopedTimer tm(c, TM_A2A); INS_TRY(peer_barrier()); }  // all peers' stores into this rank's spectrum are complete
-    return exec_inv_in<T, C>(c, S, pr);
-  }
+  INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
   if (c->p2p) {
     {
-      ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_fwd<C><<<sgrd, pblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, c->nranks, 0, 0, rows);
+      ScopedTimer tm(c, TM_SCATTER);
+      k_fft_scatter2_fwd<C><<<sgrid(rows), sblk, 0, c->stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, 0, rows);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
-    INS_TRY(peer_barrier());
+    INS_TRY(peer_barrier(c));
   } else {
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, 0);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, P, 0);
       CHECK_LAUNCH(c);
     }
     {
       ScopedTimer tm(c, TM_A2A);
       INS_NCCL(c, ncclGroupStart());
-      for (int q = 0; q < c->nranks; q++) {
+      for (int q = 0; q < P; q++) {
         const i64 ns = rows * chunk_w(q) * 2, nr = rows * c->kxl * 2;
         if (ns) INS_NCCL(c, ncclSend((T *)(B + (i64)q * c->kxc * rows), ns, dt, q, c->comm, c->stream));
         if (nr) INS_NCCL(c, ncclRecv((T *)(S + (i64)q * rows * c->kxl), nr, dt, q, c->comm, c->stream));
@@ -1000,17 +1017,17 @@ static int poisson_solve(insb200_ctx *c) {
   }
   if (c->p2p) {
     if (c->kxl > 0) {
-      ScopedTimer tm(c, TM_PACK);
-      k_fft_scatter_bwd<C><<<sgrd, pblk, 0, c->stream>>>(pS, W, c->nxp, rows, c->kxl, c->kx0, c->rank, c->nranks, 0, rows);
+      ScopedTimer tm(c, TM_SCATTER);
+      k_fft_scatter2_bwd<C><<<sgrid(rows), sblk, 0, c->stream>>>(pS, W, c->nxp, rows, c->kxl, c->kx0, c->rank, P, 0, rows);
       CHECK_LAUNCH(c);
     }
     ScopedTimer tm(c, TM_A2A);
-    INS_TRY(peer_barrier());
+    INS_TRY(peer_barrier(c));
   } else {
     {
       ScopedTimer tm(c, TM_A2A);
       INS_NCCL(c, ncclGroupStart());
-      for (int q = 0; q < c->nranks; q++) {
+      for (int q = 0; q < P; q++) {
         const i64 ns = rows * c->kxl * 2, nr = rows * chunk_w(q) * 2;
         if (ns) INS_NCCL(c, ncclSend((T *)(S + (i64)q * rows * c->kxl), ns, dt, q, c->comm, c->stream));
         if (nr) INS_NCCL(c, ncclRecv((T *)(B + (i64)q * c->kxc * rows), nr, dt, q, c->comm, c->stream));
@@ -1019,7 +1036,7 @@ static int poisson_solve(insb200_ctx *c) {
     }
     {
       ScopedTimer tm(c, TM_PACK);
-      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, 1);
+      k_fft_pack<C><<<pgrd, pblk, 0, c->stream>>>(B, S, c->nxh, c->nxp, rows, c->kxc, P, 1);
       CHECK_LAUNCH(c);
     }
   }
@@ -2142,7 +2159,8 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "smag_ty") { if (v != 8 && v != 16) INS_FAIL(c, "smag_ty must be 8 or 16"); c->smag_ty = v; }
   else if (k == "smag_zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "smag_zchunk must be 0 (automatic) or >= 2"); c->smag_zchunk = v; }
   else if (k == "p2p_halo") c->p2p_halo = v != 0;
-  else if (k == "p2p_fused") { if (v < 0 || v > 2) INS_FAIL(c, "p2p_fused must be 0, 1 or 2"); c->p2p_fused = v; }
+  else if (k == "fast_barrier") c->fast_barrier = v != 0;
+  else if (k == "p2p_fused") { if (v != 0) INS_FAIL(c, "p2p_fused: the fused peer transposes (k_zsolve_peer) are a negative result kept behind -DINSB200_EXPERIMENTAL (DESIGN.md)"); }
   else if (k == "p2p") {
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
     c->p2p_enable = v != 0;

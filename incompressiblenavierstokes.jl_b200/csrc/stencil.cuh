@@ -640,78 +640,16 @@ static __global__ void k_reduce_final(const double *part_ke, const double *part_
 // ---------------------------------------------------------------------------------------------
 template <typename C>
 __global__ void k_fft_pack(C *B, const C *__restrict__ S, int nxh, int ps /* row pitch of S */, i64 rows /* ny*nzl (or nyl in 2-D) */,
-                           int kxc, int dir /*0: S->B, 1: B->S*/) {
+                           int kxc, int nranks, int dir /*0: S->B, 1: B->S*/) {
   const int i = blockIdx.y * blockDim.x + threadIdx.x;                  // kx
   const i64 r = (i64)blockIdx.x * blockDim.y + threadIdx.y;              // row
   if (i >= nxh || r >= rows) return;
-  const int q = i / kxc;
+  const int q = min(i / max(kxc, 1), nranks - 1);
   const int kq = i - q * kxc;
-  const int w = min(kxc, nxh - q * kxc);  // width of q's chunk
+  const int w = q == nranks - 1 ? nxh - q * kxc : kxc;  // width of q's chunk (the last rank also takes the remainder)
   const i64 bo = (i64)q * kxc * rows + r * w + kq;
   if (dir == 0) B[bo] = S[r * ps + i];
   else ((C *)S)[r * ps + i] = B[bo];
-}
-
-// ---------------------------------------------------------------------------------------------
-// distributed-FFT transpose over peer memory (nranks > 1, all ranks on one NVLink / NVSwitch box):
-// pack and transfer are ONE kernel -- every rank stores its part of the spectrum straight into the
-// peers' buffers (mapped with CUDA IPC), so no staging copy and no send/recv pair is needed; a tiny
-// all-reduce afterwards is the barrier that makes the remote stores visible to their consumers.
-//   forward : local S[row][kx] (row = zl*ny + ky)      ->  peer q:  W_q[(rank*rows + row)][kx - q*kxc]   (width w_q)
-//   backward: local W[(q*rows + row)][k]  (k < kxl)     ->  peer q:  S_q[row][kx0 + k]
-// ---------------------------------------------------------------------------------------------
-struct PeerPtrs {
-  void *p[16];
-};
-
-// launch: block (64, 4), grid (ceil(rows / (4 * kScatterRows)), nranks).  blockIdx.y selects the destination
-// q = (blockIdx.y + rank + 1) mod nranks: blocks are scheduled y-major, so at any time rank r mostly talks to
-// ONE peer and the peers of the different ranks form a permutation (the staggered schedule of a ring
-// all-to-all) -- with the destination picked per element instead, all ranks hit the same peer's ingress at
-// once (measured at 8 GPUs: 1.2-1.9 ms per transpose and 0.8 ms of waiting, against 0.98 ms for NCCL).
-// Every thread row keeps kScatterRows rows in flight (tools/p2p_ipc_probe.cu: one element per thread is
-// bound by block scheduling, 1.3 ms against 0.54 ms for a 2 x 270 MB exchange).
-constexpr int kScatterRows = 4;
-
-template <typename C>
-__global__ void k_fft_scatter_fwd(PeerPtrs W, const C *__restrict__ S, int nxh, int ps, i64 rows, int kxc, int rank, int nranks,
-                                  int even, i64 rbeg, i64 rend /* row range of this launch */) {
-  int q = blockIdx.y + rank + 1;
-  if (q >= nranks) q -= nranks;
-  int w = min(kxc, nxh - q * kxc);  // width of q's chunk
-  if (w <= 0) return;
-  const int wp = even ? (w + 1) & ~1 : w;  // row pitch of W_q (rounded to 16 B when it is read by TMA)
-  const i64 r0 = rbeg + ((i64)blockIdx.x * blockDim.y + threadIdx.y) * kScatterRows;
-  const C *src = S + r0 * ps + q * kxc;
-  C *dst = reinterpret_cast<C *>(W.p[q]) + ((i64)rank * rows + r0) * wp;
-  for (int k = threadIdx.x; k < w; k += blockDim.x) {
-    C v[kScatterRows];
-#pragma unroll
-    for (int j = 0; j < kScatterRows; j++)
-      if (r0 + j < rend) v[j] = src[(i64)j * ps + k];
-#pragma unroll
-    for (int j = 0; j < kScatterRows; j++)
-      if (r0 + j < rend) dst[(i64)j * wp + k] = v[j];
-  }
-}
-
-template <typename C>
-__global__ void k_fft_scatter_bwd(PeerPtrs S, const C *__restrict__ W, int ps, i64 rows, int kxl, int kx0, int rank, int nranks,
-                                  i64 rbeg, i64 rend /* row range (of every destination's slab) of this launch */) {
-  int q = blockIdx.y + rank + 1;
-  if (q >= nranks) q -= nranks;
-  const i64 r0 = rbeg + ((i64)blockIdx.x * blockDim.y + threadIdx.y) * kScatterRows;  // row of q's slab
-  const C *src = W + ((i64)q * rows + r0) * kxl;
-  C *dst = reinterpret_cast<C *>(S.p[q]) + r0 * ps + kx0;
-  for (int k = threadIdx.x; k < kxl; k += blockDim.x) {  // local kx
-    C v[kScatterRows];
-#pragma unroll
-    for (int j = 0; j < kScatterRows; j++)
-      if (r0 + j < rend) v[j] = src[(i64)j * kxl + k];
-#pragma unroll
-    for (int j = 0; j < kScatterRows; j++)
-      if (r0 + j < rend) dst[(i64)j * ps + k] = v[j];
-  }
 }
 
 }  // namespace insb200

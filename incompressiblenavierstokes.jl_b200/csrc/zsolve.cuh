@@ -278,6 +278,7 @@ __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensor
   }
 }
 
+#ifdef INSB200_EXPERIMENTAL  // negative result kept for reference: slower than scatter kernels + k_zsolve
 // -------------------------------------------------------------------------------------------------
 // k_zsolve_peer: the same solve for a slab-decomposed grid, FUSED with both transposes of the distributed
 // FFT.  Rank r owns the kx range [kx0, kx0+kxl) for all ky and all z; the z range [q*nzl, (q+1)*nzl) of a
@@ -340,5 +341,7 @@ __global__ void __launch_bounds__(512) k_zsolve_peer(const __grid_constant__ Pee
     tma_store_commit_wait();
   }
 }
+
+#endif  // INSB200_EXPERIMENTAL
 
 }  // namespace insb200

@@ -2,8 +2,10 @@
   * ghost planes of the decomposed axis by ring send/recv == the reference's periodic apply_bc on the whole field
   * the distributed spectral Poisson solve -- in-slab transforms, pack by kx chunk, all-to-all, last-axis
     transform, symbol scaling with global wavenumbers, and back -- == psolver_spectral on the whole field.
-The array arithmetic here is NumPy (the product's is CUDA + NCCL, tested on GPUs); what is pinned is the
-decomposition logic: slab bounds, chunk widths, message layout, global index offsets."""
+The array arithmetic here is NumPy (the product's is CUDA + NVLink peer stores / NCCL, tested on GPUs); the
+DECOMPOSITION -- slab bounds and the kx ranges of the transposed spectrum -- is the product's own
+`insb200_decomposition` (pure host arithmetic of libinsb200.so, the function `insb200_create` uses), so that this test
+pins the message layout and the global index offsets the CUDA path relies on."""
 import os
 import socket
 
@@ -25,18 +27,18 @@ def _free_port():
 
 
 def slab_bounds(n_last, rank, nranks):
-    m = n_last // nranks
-    return rank * m, (rank + 1) * m
+    """The PRODUCT's decomposition (insb200_decomposition, the host arithmetic insb200_create uses; no GPU needed)."""
+    import insb200 as ins
+
+    return ins.slab_bounds(n_last, rank, nranks)
 
 
-def kx_chunk(nxh, rank, nranks, even=False):
-    """insb200_create: kxc = ceil(nxh / nranks) (rounded up to an even number in Float32 so that chunk starts are
-    16-byte aligned); rank owns kx in [rank*kxc, min((rank+1)*kxc, nxh))."""
-    kxc = (nxh + nranks - 1) // nranks
-    if even:
-        kxc = (kxc + 1) & ~1
-    lo = min(rank * kxc, nxh)
-    return kxc, lo, min((rank + 1) * kxc, nxh) - lo
+def kx_chunk(nxh, rank, nranks):
+    """(first kx, count) of `rank` in the transposed spectrum -- again the product's own arithmetic."""
+    import insb200 as ins
+
+    _, _, kx0, kxl = ins.decomposition(2 * (nxh - 1), nranks, rank, nranks)
+    return kx0, kxl
 
 
 def _worker(rank, world, port, D, n, q):
@@ -76,10 +78,10 @@ def _worker(rank, world, port, D, n, q):
         fl = np.ascontiguousarray(np.transpose(fl, [0] + list(range(D - 1, 0, -1))))  # (zl, [y,] x): x fastest
         S = np.fft.rfftn(fl, axes=tuple(range(1, D)))        # in-slab transform, kx halved & fastest
         nxh = n[0] // 2 + 1
-        kxc, kx0, kxl = kx_chunk(nxh, rank, world)
+        kx0, kxl = kx_chunk(nxh, rank, world)
         send = []
         for qk in range(world):
-            _, qlo, qw = kx_chunk(nxh, qk, world)
+            qlo, qw = kx_chunk(nxh, qk, world)
             send.append(torch.from_numpy(np.ascontiguousarray(S[..., qlo:qlo + qw])))
         recv = [torch.empty((hi - lo,) + S.shape[1:-1] + (kxl,), dtype=send[0].dtype) for _ in range(world)]
         ops = []
@@ -106,7 +108,7 @@ def _worker(rank, world, port, D, n, q):
         R = np.fft.ifft(R, axis=0)
         back_send = [torch.from_numpy(np.ascontiguousarray(R[slab_bounds(n[D - 1], qk, world)[0]:slab_bounds(n[D - 1], qk, world)[1]]))
                      for qk in range(world)]
-        back_recv = [torch.empty((hi - lo,) + S.shape[1:-1] + (kx_chunk(nxh, qk, world)[2],), dtype=send[0].dtype) for qk in range(world)]
+        back_recv = [torch.empty((hi - lo,) + S.shape[1:-1] + (kx_chunk(nxh, qk, world)[1],), dtype=send[0].dtype) for qk in range(world)]
         ops = []
         for qk in range(world):
             if qk == rank:
