@@ -517,9 +517,10 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches, ffts = lib.insb200_launch_count(h) - l0, lib.insb200_fft_exec_count(h) - f0
     graph_replays = lib.insb200_graph_replays(h) - g0
-    if sampler and w1 - w0 < 1.0:
-        # the 100 ms sampler needs a region of >= 1 s: repeat the same K steps (untimed for `value`) until it has samples
-        reps = int(np.ceil(1.2 / max(w1 - w0, 1e-3)))
+    if ms < 1000.0:
+        # the 100 ms clock sampler needs a region of >= 1 s: repeat the same K steps (untimed for `value`) until it has
+        # samples.  EVERY rank repeats (the steps are collective), the count follows from the rank-maximum `ms`
+        reps = int(np.ceil(1200.0 / max(ms, 1.0)))
         for _ in range(reps):
             ins.api._rk_steps(method, setup, u, t, dt, K, theta)
         torch.cuda.synchronize()
