@@ -51,11 +51,14 @@ __global__ void __launch_bounds__(32) k_peer_barrier(PeerPtrs F, int rank, int n
 // Transposed spectrum of rank q: W_q[(src * rows + row)][k], k < w_q, dense -- all z of its kx range.
 //   forward : S[row][q kxc + k]  ->  W_q[rank * rows + row][k]
 //   backward: W[(q * rows + row)][k] (k < w_rank)  ->  S_q[row][kx0 + k]
-// Launch: block (32, WARPS), grid (ceil(nrows / (WARPS * ROWS)), nranks).  blockIdx.y selects the destination
-// q = (blockIdx.y + rank + 1) mod nranks: blocks are scheduled y-major, so at any time the ranks talk to a permutation
-// of the peers (the staggered schedule of a ring all-to-all; all ranks hitting the same peer's ingress at once cost a
-// factor of two at 8 GPUs, profiles/r1_*).  Every warp keeps ROWS rows in flight.
-constexpr int kSc2Warps = 8, kSc2Rows = 4;
+// Launch: a PERSISTENT grid of `gridDim.x` blocks of kSc2Warps warps (set_param("scatter_blocks")).  Work item i (one
+// per warp and trip) = row group i / P for destination slot i % P, destination q = (slot + rank + 1) mod P: consecutive
+// warps serve different peers, every rank is staggered onto a different one (the schedule of a ring all-to-all; all ranks
+// hitting one peer's ingress at once cost a factor of two at 8 GPUs, profiles/r1_*), and the local part of the transpose
+// (q = rank) hides under the transfers.  Measured at 2 GPUs (profiles/r2_sweep_2gpu.txt): below 64 blocks the kernel
+// starves NVLink, above 128 it takes SMs away from the cuFFT it overlaps with.  The default transposes are pitched
+// peer copies on the copy engines (insb200.cu, transpose_ce); these kernels are the SM alternative.
+constexpr int kSc2Warps = 8, kSc2Rows = 8;
 
 template <typename C>
 struct alignas(16) CVec {
@@ -97,26 +100,34 @@ __device__ __forceinline__ void copy_rows(C *__restrict__ dst, i64 dpitch, const
 template <typename C>
 __global__ void __launch_bounds__(32 * kSc2Warps)
     k_fft_scatter2_fwd(PeerPtrs W, const C *__restrict__ S, int nxh, int ps, i64 rows, int kxc, int rank, int nranks, i64 rbeg, i64 rend) {
-  int q = blockIdx.y + rank + 1;
-  if (q >= nranks) q -= nranks;
-  const int w = q == nranks - 1 ? nxh - q * kxc : kxc;
-  if (w <= 0) return;
-  const i64 r0 = rbeg + ((i64)blockIdx.x * kSc2Warps + threadIdx.y) * kSc2Rows;
-  if (r0 >= rend) return;
-  const int nr = (int)(rend - r0 < kSc2Rows ? rend - r0 : kSc2Rows);
-  copy_rows<C>(reinterpret_cast<C *>(W.p[q]) + ((i64)rank * rows + r0) * w, w, S + r0 * ps + (i64)q * kxc, ps, w, nr, threadIdx.x);
+  const i64 ngroups = (rend - rbeg + kSc2Rows - 1) / kSc2Rows, nitems = ngroups * nranks;
+  const i64 nwarps = (i64)gridDim.x * kSc2Warps;
+  for (i64 it = (i64)blockIdx.x * kSc2Warps + threadIdx.y; it < nitems; it += nwarps) {
+    const i64 g = it / nranks;
+    int q = (int)(it - g * nranks) + rank + 1;
+    if (q >= nranks) q -= nranks;
+    const int w = q == nranks - 1 ? nxh - q * kxc : kxc;
+    if (w <= 0) continue;
+    const i64 r0 = rbeg + g * kSc2Rows;
+    const int nr = (int)(rend - r0 < kSc2Rows ? rend - r0 : kSc2Rows);
+    copy_rows<C>(reinterpret_cast<C *>(W.p[q]) + ((i64)rank * rows + r0) * w, w, S + r0 * ps + (i64)q * kxc, ps, w, nr, threadIdx.x);
+  }
 }
 
 template <typename C>
 __global__ void __launch_bounds__(32 * kSc2Warps)
     k_fft_scatter2_bwd(PeerPtrs S, const C *__restrict__ W, int ps, i64 rows, int kxl, int kx0, int rank, int nranks, i64 rbeg, i64 rend) {
-  int q = blockIdx.y + rank + 1;
-  if (q >= nranks) q -= nranks;
   if (kxl <= 0) return;
-  const i64 r0 = rbeg + ((i64)blockIdx.x * kSc2Warps + threadIdx.y) * kSc2Rows;  // row of q's slab
-  if (r0 >= rend) return;
-  const int nr = (int)(rend - r0 < kSc2Rows ? rend - r0 : kSc2Rows);
-  copy_rows<C>(reinterpret_cast<C *>(S.p[q]) + r0 * ps + kx0, ps, W + ((i64)q * rows + r0) * kxl, kxl, kxl, nr, threadIdx.x);
+  const i64 ngroups = (rend - rbeg + kSc2Rows - 1) / kSc2Rows, nitems = ngroups * nranks;
+  const i64 nwarps = (i64)gridDim.x * kSc2Warps;
+  for (i64 it = (i64)blockIdx.x * kSc2Warps + threadIdx.y; it < nitems; it += nwarps) {
+    const i64 g = it / nranks;
+    int q = (int)(it - g * nranks) + rank + 1;
+    if (q >= nranks) q -= nranks;
+    const i64 r0 = rbeg + g * kSc2Rows;  // row of q's slab
+    const int nr = (int)(rend - r0 < kSc2Rows ? rend - r0 : kSc2Rows);
+    copy_rows<C>(reinterpret_cast<C *>(S.p[q]) + r0 * ps + kx0, ps, W + ((i64)q * rows + r0) * kxl, kxl, kxl, nr, threadIdx.x);
+  }
 }
 
 // ---- halo planes --------------------------------------------------------------------------------------------------

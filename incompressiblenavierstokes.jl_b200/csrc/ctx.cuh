@@ -85,7 +85,7 @@ struct insb200_ctx {
   int tile_y = 16;         // tiled stage kernel: 32 x tile_y cells per block
   int fft_pipe = 4;        // param: nranks > 1, peer transposes: the slab is transformed in this many z-chunks and the scatter of
                            // one chunk overlaps the cuFFT of the next on a second stream (1 = no pipelining)
-  int fft_pipe_min_ranks = 4;
+  int fft_pipe_min_ranks = 2;
   cudaStream_t comm_stream = nullptr;
   cudaEvent_t pipe_ev[16] = {nullptr}, pipe_sync = nullptr;
   int fft_chunk = 0;       // param: planes per in-plane cuFFT exec (0 = the whole slab); small chunks keep the x->y intermediate in L2
@@ -146,6 +146,10 @@ struct insb200_ctx {
   void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter (NCCL fallback)
   void *flagbuf = nullptr, *peerF[16] = {nullptr};      // barrier flag words of this rank / of every rank (CUDA IPC): k_peer_barrier
   unsigned bar_epoch = 0;                               // barriers issued so far (same sequence on every rank)
+  int transpose_ce = 1;                                 // param "transpose_ce": 1 = transposes as pitched peer copies on the copy engines, 0 = scatter kernels
+  std::vector<cudaStream_t> ce_streams;                 // one stream per destination slot of the copy-engine transposes
+  std::vector<cudaEvent_t> ce_events;                   // [chunk][destination slot]
+  int scatter_blocks = 128;                             // param "scatter_blocks": blocks of the persistent transpose kernels (comm.cuh)
   int fast_barrier = 1;                                 // param "fast_barrier": 0 = ncclAllReduce barriers
   void *ztw = nullptr;                                  // twiddles exp(-2 pi i t / n_last) of k_zsolve (complex T)
   void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)

@@ -310,10 +310,13 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
     if (c->plan_inv_in) cufftDestroy(c->plan_inv_in);
     if (c->plan_last) cufftDestroy(c->plan_last);
   }
+  for (auto &st : c->ce_streams) if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+  for (auto &e : c->ce_events) if (e) cudaEventDestroy(e);
   if (c->p2p) {  // unmap the peers' buffers (every rank synchronised its stream above; destroy is collective)
     for (int q = 0; q < 16; q++) {
       if (q != c->rank && c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
       if (q != c->rank && c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
+      if (q != c->rank && c->peerF[q]) cudaIpcCloseMemHandle(c->peerF[q]);
     }
   }
   for (auto &kv : c->halo_peers) {
@@ -327,6 +330,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
     cudaStreamDestroy(c->comm_stream);
   }
   if (c->barbuf) cudaFree(c->barbuf);
+  if (c->flagbuf) cudaFree(c->flagbuf);
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
@@ -903,21 +907,66 @@ static int poisson_solve(insb200_ctx *c) {
   auto chunk_w = [&](int q) { return q == P - 1 ? c->nxh - q * c->kxc : c->kxc; };
   dim3 pblk(64, 4, 1), pgrd((unsigned)((rows + 3) / 4), (c->nxh + 63) / 64, 1);
   dim3 sblk(32, kSc2Warps, 1);
-  auto sgrid = [&](i64 nr) { return dim3((unsigned)((nr + kSc2Warps * kSc2Rows - 1) / (kSc2Warps * kSc2Rows)), P, 1); };
-  const bool pipelined = c->p2p && D == 3 && zsolve_supported(c) && c->fft_pipe > 1 && c->fft_batch * c->fft_pipe == c->nloc[2];
+  auto sgrid = [&](i64 nr) {  // persistent scatter grid: at most `scatter_blocks` blocks (comm.cuh)
+    const i64 need = ((nr + kSc2Rows - 1) / kSc2Rows * P + kSc2Warps - 1) / kSc2Warps;
+    return dim3((unsigned)std::max<i64>(1, std::min<i64>(need, c->scatter_blocks)), 1, 1);
+  };
+  const bool pipelined = c->p2p && D == 3 && zsolve_supported(c) && c->fft_batch > 0 && c->nloc[2] % c->fft_batch == 0;
   C *W = c->p2p ? B : S;  // the transposed spectrum (kxl fastest, ky, global z) of this rank
   PeerPtrs pS, pB;
   for (int q = 0; q < 16; q++) { pS.p[q] = c->peerS[q]; pB.p[q] = c->peerB[q]; }
   if (pipelined) {
-    // ---- pipelined: the slab is transformed in fft_pipe z-chunks; the peer scatter of chunk b runs on a second
-    // stream while cuFFT works on chunk b+1 (forward), and the C2R of chunk b while chunk b+1 is scattered back
-    const int NB = c->fft_pipe;
+    // ---- pipelined: the slab is transformed in NB z-chunks (NB = 1: the whole slab); the transpose of chunk b runs
+    // while cuFFT works on chunk b+1 (forward), and the C2R of chunk b while chunk b+1 travels back.
+    // transpose_ce = 1 (default): the transposes are PITCHED PEER COPIES on the copy engines, one stream per destination
+    // (cudaMemcpy2DAsync into the peers' IPC-mapped buffers): no SM is taken away from cuFFT, and a pitched copy moves
+    // 663 GB/s where SM stores of the same rows reach 555 (tools/p2p_probe.cu, profiles/r1_p2p_probe_2xB200.txt).
+    // transpose_ce = 0: the persistent scatter kernels of comm.cuh on one second stream.
+    const int NB = c->nloc[2] / c->fft_batch;
     const i64 rb = (i64)c->fft_batch * c->nloc[1];  // rows per chunk
+    if (NB > 16) INS_FAIL(c, "more than 16 transform chunks");
     if (!c->comm_stream) {
       INS_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
       for (int b = 0; b < 16; b++) INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_ev[b], cudaEventDisableTiming));
       INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_sync, cudaEventDisableTiming));
     }
+    const bool ce = c->transpose_ce != 0;
+    if (ce && c->ce_streams.empty()) {
+      c->ce_streams.resize(P);
+      for (int d = 0; d < P; d++) INS_CUDA(c, cudaStreamCreateWithFlags(&c->ce_streams[d], cudaStreamNonBlocking));
+      c->ce_events.resize((size_t)16 * P);
+      for (auto &e : c->ce_events) INS_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    // transpose of chunk b after event `after`; fwd: S -> peers' B, bwd: B -> peers' S.  Afterwards comm_stream has
+    // waited for every piece of the chunk (so an event recorded there means "chunk b has left this rank").
+    auto transpose_chunk = [&](int b, bool fwd, cudaEvent_t after) -> int {
+      INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, after, 0));
+      ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
+      const i64 r0 = b * rb;
+      if (!ce) {
+        if (fwd) k_fft_scatter2_fwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, r0, r0 + rb);
+        else if (c->kxl > 0) k_fft_scatter2_bwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, P, r0, r0 + rb);
+        CHECK_LAUNCH(c);
+        return 0;
+      }
+      for (int d = 0; d < P; d++) {
+        const int q = (d + c->rank + 1) % P;  // every rank starts with a different peer
+        const int w = fwd ? chunk_w(q) : c->kxl;
+        if (w <= 0) continue;
+        cudaStream_t st = c->ce_streams[d];
+        INS_CUDA(c, cudaStreamWaitEvent(st, after, 0));
+        if (fwd)
+          INS_CUDA(c, cudaMemcpy2DAsync((C *)c->peerB[q] + ((i64)c->rank * rows + r0) * w, (size_t)w * sizeof(C), S + r0 * c->nxp + (i64)q * c->kxc,
+                                        (size_t)c->nxp * sizeof(C), (size_t)w * sizeof(C), (size_t)rb, cudaMemcpyDeviceToDevice, st));
+        else
+          INS_CUDA(c, cudaMemcpy2DAsync((C *)c->peerS[q] + r0 * c->nxp + c->kx0, (size_t)c->nxp * sizeof(C), B + ((i64)q * rows + r0) * w,
+                                        (size_t)w * sizeof(C), (size_t)w * sizeof(C), (size_t)rb, cudaMemcpyDeviceToDevice, st));
+        cudaEvent_t ev = c->ce_events[(size_t)b * P + d];
+        INS_CUDA(c, cudaEventRecord(ev, st));
+        INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, ev, 0));
+      }
+      return 0;
+    };
     {
       ScopedTimer tm(c, TM_FFT_FWD);
       for (int b = 0; b < NB; b++) {
@@ -926,10 +975,7 @@ static int poisson_solve(insb200_ctx *c) {
         if (sizeof(T) == 4) INS_CUFFT(c, cufftExecR2C(c->plan_fwd_in, (cufftReal *)r, (cufftComplex *)s));
         else INS_CUFFT(c, cufftExecD2Z(c->plan_fwd_in, (cufftDoubleReal *)r, (cufftDoubleComplex *)s));
         INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->stream));
-        INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_ev[b], 0));
-        ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
-        k_fft_scatter2_fwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, b * rb, (b + 1) * rb);
-        CHECK_LAUNCH(c);
+        INS_TRY(transpose_chunk(b, true, c->pipe_ev[b]));
       }
       c->fft_execs++;
     }
@@ -941,13 +987,8 @@ static int poisson_solve(insb200_ctx *c) {
     }
     if (c->kxl > 0) INS_TRY((launch_zsolve<T>(c, B, (i64)c->nglob[1] * c->kxl, c->kxl, c->kx0, invN)));
     INS_CUDA(c, cudaEventRecord(c->pipe_sync, c->stream));
-    INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->pipe_sync, 0));
     for (int b = 0; b < NB; b++) {
-      if (c->kxl > 0) {
-        ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
-        k_fft_scatter2_bwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, P, b * rb, (b + 1) * rb);
-        CHECK_LAUNCH(c);
-      }
+      INS_TRY(transpose_chunk(b, false, c->pipe_sync));
       INS_CUDA(c, cudaEventRecord(c->pipe_ev[b], c->comm_stream));
     }
     {
@@ -2160,6 +2201,8 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "smag_zchunk") { if (v != 0 && v < 2) INS_FAIL(c, "smag_zchunk must be 0 (automatic) or >= 2"); c->smag_zchunk = v; }
   else if (k == "p2p_halo") c->p2p_halo = v != 0;
   else if (k == "fast_barrier") c->fast_barrier = v != 0;
+  else if (k == "transpose_ce") c->transpose_ce = v != 0;
+  else if (k == "scatter_blocks") { if (v < 1 || v > 65535) INS_FAIL(c, "scatter_blocks must be in [1, 65535]"); c->scatter_blocks = v; }
   else if (k == "p2p_fused") { if (v != 0) INS_FAIL(c, "p2p_fused: the fused peer transposes (k_zsolve_peer) are a negative result kept behind -DINSB200_EXPERIMENTAL (DESIGN.md)"); }
   else if (k == "p2p") {
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
