@@ -134,6 +134,18 @@ int insb200_kinetic_energy(insb200_ctx *ctx, const void *u, double *E);
 /* maximum(abs, u) of timelogger: src/processors.jl:67 */
 int insb200_maxabs(insb200_ctx *ctx, const void *u, double *m);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The fused reduction pass of the three
+ * entries above without any allocation, host copy or synchronisation: out4_dev is a caller-owned DEVICE buffer of four
+ * doubles that receives { total kinetic energy, max|u_1|, max|u_2|, max|u_3| } (the inputs of insb200_kinetic_energy,
+ * insb200_maxabs and the CFL bound), enqueued on the context's stream.  The per-block partial sums live in a static
+ * 2 MiB device array inside the library (held by every GPU that loads it until the process exits) that ALL calls and
+ * all contexts on a device share: calls that overlap on the GPU (different streams) race; calls on one stream are safe.
+ * Limit: 65536 blocks of 64 x 4 cells, i.e. grids up to 256^3 (3-D) or 4096^2 (2-D); larger grids and nranks > 1 are
+ * rejected with an error message.  The first call on a device looks the array's address up once
+ * (cudaGetSymbolAddress): make one warm-up call before capturing a graph. */
+int insb200_reduce_noalloc(insb200_ctx *ctx, const void *u, double *out4_dev);
+
 /* ---- time stepping -------------------------------------------------------------------------- */
 
 /* timestep!(::ExplicitRungeKuttaMethod, stepper, dt; theta, cache):

@@ -40,6 +40,7 @@ PROTOTYPES = {
     "insb200_cfl_dt": (c_int, [c_void_p, c_void_p, P(c_double)]),
     "insb200_kinetic_energy": (c_int, [c_void_p, c_void_p, P(c_double)]),
     "insb200_maxabs": (c_int, [c_void_p, c_void_p, P(c_double)]),
+    "insb200_reduce_noalloc": (c_int, [c_void_p, c_void_p, c_void_p]),
     "insb200_rk_step": (c_int, [c_void_p, c_void_p, c_double, c_double, c_int, P(c_double), P(c_double), c_double, c_void_p]),
     "insb200_rk_steps": (c_int, [c_void_p, c_void_p, P(c_double), c_double, c_int, c_int, P(c_double), P(c_double), c_double, P(c_double)]),
     "insb200_solve_unsteady_host": (c_int, [c_void_p, c_void_p, c_double, c_double, c_double, c_double, c_int, c_int, c_int,

@@ -1348,6 +1348,58 @@ static int op_reduce(insb200_ctx *c, const void *u, double *out4) {
 
 }  // namespace insb200
 
+// ---- reductions without any allocation (no reference counterpart) ----
+// insb200_reduce_noalloc: the fused reduction pass of insb200_kinetic_energy / insb200_maxabs / insb200_cfl_dt
+// (k_reduce_partials + k_reduce_final, unchanged) for callers that cannot call cudaMalloc -- code under CUDA graph
+// capture, tight serving loops, harnesses that forbid it.  The per-block partials live in the file-scope device array
+// below instead of the context's workspace, the result goes to a caller-owned DEVICE buffer, nothing is copied to the
+// host and nothing is synchronised.  kNoAllocMaxBlocks blocks of 64 x 4 cells: up to 256^3 in 3-D, 4096^2 in 2-D
+// (2 MiB of device memory on every GPU that loads the library, until the process exits).
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current (noalloc_scratch below).
+namespace insb200 {
+constexpr long long kNoAllocMaxBlocks = 65536;
+static __device__ __align__(256) double g_noalloc_scratch[4 * kNoAllocMaxBlocks];
+static double *g_noalloc_ptr[64] = {nullptr};  // device address of g_noalloc_scratch, per device ordinal
+
+static int noalloc_scratch(insb200_ctx *c, double **out) {
+  if (c->device < 0 || c->device >= 64) INS_FAIL(c, "insb200_reduce_noalloc: device ordinal out of range");
+  if (!g_noalloc_ptr[c->device]) {  // the context's device is current (CHECK_CTX)
+    void *ptr = nullptr;
+    INS_CUDA(c, cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+    g_noalloc_ptr[c->device] = (double *)ptr;
+  }
+  *out = g_noalloc_ptr[c->device];
+  return 0;
+}
+
+template <typename T, int D>
+static int op_reduce_noalloc(insb200_ctx *c, const void *u, double *out4_dev) {
+  dim3 grd = cell_grid(c->nloc);
+  const i64 nb = (i64)grd.x * grd.y * grd.z;
+  if (nb > kNoAllocMaxBlocks)
+    INS_FAIL(c, "insb200_reduce_noalloc: grid too large for the static scratch array (" + std::to_string(nb) + " blocks of 64 x 4 cells, maximum " +
+                    std::to_string(kNoAllocMaxBlocks) + ": up to 256^3 or 4096^2 cells); use insb200_kinetic_energy / insb200_maxabs");
+  double *scr = nullptr;
+  INS_TRY(noalloc_scratch(c, &scr));
+  // every block writes its own slot and k_reduce_final reads exactly nb slots: nothing has to start at zero, stale
+  // contents of an earlier (larger) call are never read
+  double *part_ke = scr, *part_max = scr + nb;
+  k_reduce_partials<T, D><<<grd, cell_block(), 0, c->stream>>>(view_ghosted_c<T>(c, u), geo_ghosted(c), volume<T>(c), part_ke, part_max);
+  CHECK_LAUNCH(c);
+  k_reduce_final<<<1, 1024, 0, c->stream>>>(part_ke, part_max, nb, out4_dev);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+}  // namespace insb200
+
+extern "C" int insb200_reduce_noalloc(insb200_ctx *c, const void *u, double *out4_dev) {
+  CHECK_CTX(c);
+  if (!u || !out4_dev) INS_FAIL(c, "insb200_reduce_noalloc: NULL pointer");
+  if (c->nranks > 1) INS_FAIL(c, "insb200_reduce_noalloc: one rank only (the all-reduced reductions are insb200_kinetic_energy / insb200_maxabs)");
+  return DISPATCH(c, op_reduce_noalloc, c, u, out4_dev);
+}
+
 #define API_PROLOG(c) CHECK_CTX(c)
 
 extern "C" int insb200_apply_bc_u(insb200_ctx *c, void *u) {
