@@ -81,6 +81,19 @@ int insb200_apply_bc_p(insb200_ctx *ctx, void *p);
  * (src/operators.jl:861-879).  `f` = device vector field in reference layout, copied; NULL clears. */
 int insb200_set_bodyforce(insb200_ctx *ctx, const void *f);
 
+/* Unsteady body force, the `issteadybodyforce = false` branch of applybodyforce! (src/operators.jl:870-877:
+ * `Fα .+= bodyforce.(α, xin..., t)` at every call).  The library cannot evaluate the caller's function, so the caller
+ * does -- with the reference's own broadcast -- whenever the path needs the force at a new time: `fn(user, t, &field)`
+ * must set `field` to a DEVICE vector field in the reference layout that holds bodyforce.(α, xu[α]..., t) over the whole
+ * array (ghosts included, as the broadcast of the reference), valid until the next invocation, with the work that fills
+ * it either complete or enqueued on the context's stream; return 0, anything else aborts the calling entry point.
+ * It is invoked once per RK stage at the stage's time (momentum!(ku[i], u, temp, t, setup),
+ * src/time_steppers/step_explicit_runge_kutta.jl:21,32: tstart for the first stage, tstart + c[i-1] dt afterwards) and
+ * by insb200_momentum / insb200_pressure at their `t`.  Steps with a callback are not replayed as CUDA graphs.
+ * fn = NULL removes the callback (and the force). */
+typedef int (*insb200_force_fn)(void *user, double t, const void **field);
+int insb200_set_bodyforce_callback(insb200_ctx *ctx, insb200_force_fn fn, void *user);
+
 /* momentum!(F, u, temp=nothing, t, setup): src/operators.jl:967-976 (fill! + convectiondiffusion!
  * :634-690 + applybodyforce! :861-879).  Ghosts of u must be valid; ghosts of F are 0, or the
  * ghost values of the stored force field (`F .+= bodyforce` covers the whole array). */

@@ -13,6 +13,9 @@ LIB_PATH = os.path.join(HERE, "lib", "libinsb200.so")
 c_void_p, c_int, c_double, c_ll = C.c_void_p, C.c_int, C.c_double, C.c_longlong
 P = C.POINTER
 
+# insb200_force_fn: int (*)(void *user, double t, const void **field)
+FORCE_FN = C.CFUNCTYPE(c_int, c_void_p, c_double, P(c_void_p))
+
 # name -> (restype, argtypes); mirrors include/insb200.h declaration by declaration
 PROTOTYPES = {
     "insb200_version": (c_int, []),
@@ -27,6 +30,7 @@ PROTOTYPES = {
     "insb200_apply_bc_u": (c_int, [c_void_p, c_void_p]),
     "insb200_apply_bc_p": (c_int, [c_void_p, c_void_p]),
     "insb200_set_bodyforce": (c_int, [c_void_p, c_void_p]),
+    "insb200_set_bodyforce_callback": (c_int, [c_void_p, FORCE_FN, c_void_p]),
     "insb200_momentum": (c_int, [c_void_p, c_void_p, c_void_p, c_double]),
     "insb200_convectiondiffusion": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     "insb200_smagorinsky": (c_int, [c_void_p, c_void_p, c_void_p, c_double]),

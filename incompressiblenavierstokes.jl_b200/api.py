@@ -190,23 +190,43 @@ def Setup(x, boundary_conditions=None, bodyforce=None, issteadybodyforce=True, c
         ctx.call("insb200_set_temperature", float(T(q.alpha1)), float(T(q.alpha2)), float(T(q.alpha3)), float(T(q.alpha4)),
                  float(T(q.gamma)), int(bool(q.dodissipation)), int(q.gdir))
     if bodyforce is not None:
-        if not issteadybodyforce:
-            raise NotImplementedError("only steady body forces are on the B200 hot path (setup.jl:25-32)")
-        # setup.jl:25-32 / operators.jl:870-877: F[.., a] = bodyforce(a, xu[a]..., 0) over the whole array
-        F = np.zeros(N + (D,), dtype=T, order="F")
-        for a in range(D):
-            xin = []
-            for b in range(D):
-                sh = [1] * D
-                sh[b] = -1
-                xin.append(grid.xu[a][b].reshape(sh))
-            # scalar broadcast `bodyforce.(a, x..., t)` like Julia: one scalar call per point (an
-            # array call could take NumPy's SIMD sin/cos path, which differs in the last bit)
-            val = np.vectorize(lambda *xs, _a=a: bodyforce(_a + 1, *xs, T(0)), otypes=[T])(*np.broadcast_arrays(*xin))
-            F[..., a] = val.astype(T)
-        setup.bodyforce = to_device(F, setup)
-        setup.issteadybodyforce = True
-        ctx.call("insb200_set_bodyforce", _ptr(setup.bodyforce))
+        def force_field(t):
+            # setup.jl:25-32 / operators.jl:870-877: F[.., a] = bodyforce(a, xu[a]..., t) over the whole array
+            F = np.zeros(N + (D,), dtype=T, order="F")
+            for a in range(D):
+                xin = []
+                for b in range(D):
+                    sh = [1] * D
+                    sh[b] = -1
+                    xin.append(grid.xu[a][b].reshape(sh))
+                # scalar broadcast `bodyforce.(a, x..., t)` like Julia: one scalar call per point (an
+                # array call could take NumPy's SIMD sin/cos path, which differs in the last bit)
+                val = np.vectorize(lambda *xs, _a=a: bodyforce(_a + 1, *xs, T(t)), otypes=[T])(*np.broadcast_arrays(*xin))
+                F[..., a] = val.astype(T)
+            return to_device(F, setup)
+
+        if issteadybodyforce:
+            setup.bodyforce = force_field(0)
+            setup.issteadybodyforce = True
+            ctx.call("insb200_set_bodyforce", _ptr(setup.bodyforce))
+        else:
+            # unsteady force (operators.jl:870-877): the library asks for bodyforce.(a, x..., t) at every stage time;
+            # this host mirror evaluates the Python callable on the host and uploads the field (a Julia caller
+            # broadcasts on the device)
+            setup.bodyforce = bodyforce
+            setup.issteadybodyforce = False
+
+            def _cb(user, t, field_out):
+                try:
+                    setup._force_now = force_field(t)  # kept alive until the next invocation; the upload is synchronous
+                    field_out[0] = setup._force_now.data_ptr()
+                    return 0
+                except Exception as e:  # noqa: BLE001 -- never raise across the C boundary
+                    setup._force_error = e
+                    return 1
+
+            setup._force_cb = _lib.FORCE_FN(_cb)  # keep the trampoline alive as long as the setup
+            ctx.call("insb200_set_bodyforce_callback", setup._force_cb, None)
     return setup
 
 

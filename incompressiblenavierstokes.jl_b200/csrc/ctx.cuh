@@ -125,6 +125,9 @@ struct insb200_ctx {
   void *ubuf[3] = {nullptr, nullptr, nullptr};          // rotating state buffers (compact vector)
   void *kbuf[INSB200_MAX_STAGES] = {nullptr};           // stage derivatives
   void *force = nullptr;                                // compact steady body force (nullable)
+  insb200_force_fn force_cb = nullptr;                  // unsteady body force (operators.jl:870-877): the caller evaluates it per stage time
+  void *force_user = nullptr;
+  double t_step = 0;                                    // start time of the RK step being taken (the stage times of the callback)
   void *force_g = nullptr;                              // the same force in the reference layout (ghost values of F)
   void *sigma = nullptr;                                // compact symmetric tensor, D(D+1)/2 comps
   void *sbuf = nullptr;                                 // closure term s = div sigma (vector, TMA path)
@@ -230,6 +233,13 @@ inline int fail(insb200_ctx *c, const char *file, int line, const std::string &m
     if (r_ != ncclSuccess)                                                                      \
       return ::insb200::fail((ctx), __FILE__, __LINE__, std::string("NCCL: ") + ncclGetErrorString(r_) + " in " #call); \
   } while (0)
+#ifndef CHECK_LAUNCH
+#define CHECK_LAUNCH(c)                      \
+  do {                                       \
+    (c)->launches++;                         \
+    INS_CUDA((c), cudaGetLastError());       \
+  } while (0)
+#endif
 #define INS_TRY(call)            \
   do {                           \
     int r__ = (call);            \

@@ -6,14 +6,10 @@
 
 #include "fast.cuh"
 #include "fast_stage.cuh"
+#include "zsolve_launch.cuh"
 
 namespace insb200 {
 
-#define CHECK_LAUNCH(c)                      \
-  do {                                       \
-    (c)->launches++;                         \
-    INS_CUDA((c), cudaGetLastError());       \
-  } while (0)
 
 bool stage_fast_supported(const insb200_ctx *c, bool smag) {
   if (c->D != 3 || !c->padded || c->exact) return false;
@@ -78,6 +74,13 @@ int launch_stage_fast(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double th
   return gen ? LSF(false, false, true) : LSF(false, false, false);
 #undef LSF
 }
+
+template <typename T>
+int launch_zsolve_fast(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad) {
+  return launch_zsolve_cols<T, 1>(c, S, ncols, nxw, kx0, invN, rad);
+}
+template int launch_zsolve_fast<float>(insb200_ctx *, void *, i64, int, int, float, const ZRadix &);
+template int launch_zsolve_fast<double>(insb200_ctx *, void *, i64, int, int, double, const ZRadix &);
 
 template int launch_stage_fast<float>(insb200_ctx *, const TmaStageArgs<float> &, Geo, double, const void *, const void *);
 template int launch_stage_fast<double>(insb200_ctx *, const TmaStageArgs<double> &, Geo, double, const void *, const void *);

@@ -18,4 +18,9 @@ template <typename T>
 int launch_stage_fast(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double theta, const void *ubase, const void *pbase);
 bool stage_fast_supported(const insb200_ctx *c, bool smag);
 
+// fast.cu: k_zsolve (zsolve.cuh) built with FMA contraction
+struct ZRadix;
+template <typename T>
+int launch_zsolve_fast(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad);
+
 }  // namespace insb200

@@ -14,6 +14,7 @@
 #include "tma_stage_x2.cuh"
 #include "stage2d.cuh"
 #include "zsolve.cuh"
+#include "zsolve_launch.cuh"
 #include "comm.cuh"
 #include "fast.cuh"
 
@@ -104,11 +105,6 @@ static double sinpi01(double x) {  // x in [0,1]; reduced so that multiples of 1
   ((c)->dtype == INSB200_F32 ? ((c)->D == 2 ? FN<float, 2>(__VA_ARGS__) : FN<float, 3>(__VA_ARGS__)) \
                              : ((c)->D == 2 ? FN<double, 2>(__VA_ARGS__) : FN<double, 3>(__VA_ARGS__)))
 
-#define CHECK_LAUNCH(c)                      \
-  do {                                       \
-    (c)->launches++;                         \
-    INS_CUDA((c), cudaGetLastError());       \
-  } while (0)
 
 #define CHECK_CTX(c) \
   if (!(c)) return 1; \
@@ -589,9 +585,7 @@ static int fill_ghosts(insb200_ctx *c, void *base, int nc, int wm, int wp) {
   return halo_compact<T>(c, base, nc, wm, wp);
 }
 
-typedef CUresult (*PFN_tmap_encode)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
 
 // descriptor of a padded buffer with nc components, box = (box_x, box_y, 1, nc)
 int get_tmap(insb200_ctx *c, const void *base, int nc, int box_x, int box_y, CUtensorMap *out) {
@@ -707,45 +701,6 @@ static bool zsolve_supported(const insb200_ctx *c) {
   return c->D == 3 && c->zsolve && nz >= 8 && nz <= 2048 && (nz & (nz - 1)) == 0;
 }
 
-template <typename T, int COLS>
-static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad) {
-  const int nz = c->nglob[2];
-  const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + (size_t)nz * sizeof(T) + 16;
-  auto kern = k_zsolve<T, COLS>;
-  // 2-D descriptor of the spectrum seen as [nz][2*ncols] words of T, box = (2*COLS) x min(nz, 256)
-  CUtensorMap tm;
-  {
-    auto key = std::make_tuple((const void *)S, -COLS, (int)(ncols & 0x7fffffff));
-    auto it = c->tmaps.find(key);
-    if (it != c->tmaps.end()) tm = it->second;
-    else {
-      void *fn = nullptr;
-      cudaDriverEntryPointQueryResult qr;
-      INS_CUDA(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
-      if (!fn || qr != cudaDriverEntryPointSuccess) INS_FAIL(c, "cuTensorMapEncodeTiled is not available from the driver");
-      cuuint64_t dims[2] = {(cuuint64_t)(2 * ncols), (cuuint64_t)nz};
-      cuuint64_t strides[1] = {(cuuint64_t)(2 * ncols) * sizeof(T)};
-      cuuint32_t box[2] = {(cuuint32_t)(2 * COLS), (cuuint32_t)std::min(nz, 256)};
-      cuuint32_t estr[2] = {1, 1};
-      CUresult r = ((PFN_tmap_encode)fn)(&tm, sizeof(T) == 8 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT64 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, S,
-                                         dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
-                                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-      if (r != CUDA_SUCCESS) INS_FAIL(c, "cuTensorMapEncodeTiled (spectrum) failed with CUresult " + std::to_string((int)r));
-      c->tmaps[key] = tm;
-    }
-  }
-  static size_t attr = 0;
-  if (smem > attr) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = smem;
-  }
-  const unsigned nb = (unsigned)((ncols + COLS - 1) / COLS);
-  kern<<<nb, c->zthreads, smem, c->stream>>>(tm, (const Cx<T> *)c->ztw, (const T *)c->ahat[0], (const T *)c->ahat[1],
-                                     (const T *)c->ahat[2], nz, ncols, nxw, kx0, T(-1) / invN, rad);
-  CHECK_LAUNCH(c);
-  return 0;
-}
-
 // twiddle table exp(-2 pi i t / nz) (Float64 on the host, stored in T) and the radix plan of the last axis
 template <typename T>
 static int zsolve_prepare(insb200_ctx *c, ZRadix &rad) {
@@ -780,16 +735,12 @@ static int zsolve_prepare(insb200_ctx *c, ZRadix &rad) {
 template <typename T>
 static int launch_zsolve(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN) {
   ScopedTimer tm(c, TM_POISSON_SCALE);
-  const int nz = c->nglob[2];
   ZRadix rad;
   INS_TRY((zsolve_prepare<T>(c, rad)));
-  const size_t col_bytes = (size_t)nz * sizeof(Cx<T>);
-  if (c->zcols == 4) return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
-  if (c->zcols == 16 && 16 * col_bytes <= 131072) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);  // explicit request only
-  if (c->zcols == 8 && 8 * col_bytes <= 131072) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
-  if (16 * col_bytes <= 65536) return launch_zsolve_i<T, 16>(c, S, ncols, nxw, kx0, invN, rad);
-  if (8 * col_bytes <= 65536) return launch_zsolve_i<T, 8>(c, S, ncols, nxw, kx0, invN, rad);
-  return launch_zsolve_i<T, 4>(c, S, ncols, nxw, kx0, invN, rad);
+  // default: the instantiation of fast.cu (FMA contraction on -- an FFT butterfly has nothing to be bit-identical
+  // with); set_param("exact", 1): the one of this translation unit (-fmad=false)
+  if (!c->exact) return launch_zsolve_fast<T>(c, S, ncols, nxw, kx0, invN, rad);
+  return launch_zsolve_cols<T, 0>(c, S, ncols, nxw, kx0, invN, rad);
 }
 
 #ifdef INSB200_EXPERIMENTAL
@@ -1104,6 +1055,23 @@ static int op_set_bodyforce(insb200_ctx *c, const void *f) {
   INS_TRY(dev_alloc(c, &c->force_g, (size_t)e * sizeof(T)));
   INS_CUDA(c, cudaMemcpyAsync(c->force_g, f, (size_t)e * sizeof(T), cudaMemcpyDeviceToDevice, c->stream));
   return import_field<T, D>(c, c->force, f, D);
+}
+
+// unsteady body force: ask the caller for bodyforce.(a, x..., t) (insb200_set_bodyforce_callback) and take it as the
+// stored force of the launches that follow
+template <typename T, int D>
+static int update_unsteady_force(insb200_ctx *c, double t) {
+  if (!c->force_cb) return 0;
+  const void *f = nullptr;
+  const int rc = c->force_cb(c->force_user, t, &f);
+  if (rc != 0 || !f) INS_FAIL(c, "the body-force callback failed (returned " + std::to_string(rc) + (f ? ")" : ", no field)"));
+  return op_set_bodyforce<T, D>(c, f);
+}
+// time of RK stage i of the step that starts at c->t_step: `t = tstart + c[i] * dt` is set AFTER momentum! of stage i
+// (step_explicit_runge_kutta.jl:21,32), arithmetic in T
+template <typename T>
+static double stage_time(const insb200_ctx *c, const double *cc, int i, double dt) {
+  return i == 0 ? (double)T(c->t_step) : (double)(T(c->t_step) + T(cc[i - 1]) * T(dt));
 }
 
 // F = convdiff(u) [+ force], written to any view
@@ -1425,9 +1393,18 @@ extern "C" int insb200_set_bodyforce(insb200_ctx *c, const void *f) {
   }
   return DISPATCH(c, op_set_bodyforce, c, f);
 }
-extern "C" int insb200_momentum(insb200_ctx *c, void *F, const void *u, double) {
+extern "C" int insb200_set_bodyforce_callback(insb200_ctx *c, insb200_force_fn fn, void *user) {
+  API_PROLOG(c);
+  clear_graphs(c);
+  c->force_cb = fn;
+  c->force_user = user;
+  if (!fn) return insb200_set_bodyforce(c, nullptr);
+  return 0;
+}
+extern "C" int insb200_momentum(insb200_ctx *c, void *F, const void *u, double t) {
   API_PROLOG(c);
   if (!F || !u) INS_FAIL(c, "NULL field");
+  if (c->force_cb) INS_TRY(DISPATCH(c, update_unsteady_force, c, t));
   return DISPATCH(c, op_momentum, c, F, u, 3, true);
 }
 extern "C" int insb200_convectiondiffusion(insb200_ctx *c, void *F, const void *u, int terms) {
@@ -1499,9 +1476,10 @@ extern "C" int insb200_project(insb200_ctx *c, void *u, void *p) {
   if (!u) INS_FAIL(c, "NULL field");
   return DISPATCH(c, op_project, c, u, p);
 }
-extern "C" int insb200_pressure(insb200_ctx *c, void *p, const void *u, double) {
+extern "C" int insb200_pressure(insb200_ctx *c, void *p, const void *u, double t) {
   API_PROLOG(c);
   if (!p || !u) INS_FAIL(c, "NULL field");
+  if (c->force_cb) INS_TRY(DISPATCH(c, update_unsteady_force, c, t));
   return DISPATCH(c, op_pressure, c, p, u);
 }
 extern "C" int insb200_cfl_dt(insb200_ctx *c, const void *u, double *dt) {
@@ -1804,6 +1782,7 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
       std::swap(c->preal, c->preal2);  // p of the previous stage -> preal2; preal receives the new right-hand side
       pbase = c->preal2;
     }
+    if (c->force_cb) INS_TRY((update_unsteady_force<T, 3>(c, stage_time<T>(c, tb.c, i, dt))));
     int nkrow = 0;  // earlier stage derivatives this tableau row reads
     for (int j = 0; j < i; j++) nkrow += tb.A[i * tb.s + j] != 0.0;
     // fused closure + stage kernel (fast.cu) for rows with at most 3 earlier k_j; `exact` and longer rows keep the two kernels below
@@ -1901,6 +1880,7 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
   bool pending = false;  // ubuf[cur] holds u' of the previous stage, its gradient correction is still in preal
   for (int i = 0; i < tb.s; i++) {
     const int nxt = (cur == 1) ? 2 : 1;
+    if (c->force_cb) INS_TRY((update_unsteady_force<T, D>(c, stage_time<T>(c, tb.c, i, dt))));
     // apply_bc_u! before momentum (step_explicit_runge_kutta.jl:19): wrap by index, halos over NCCL
     if (!pending) INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, 1, 1)));  // (pending: exchanged after the stage kernel)
     if (smag) INS_TRY((compute_sigma<T, D>(c, view_compact_c<T>(c, c->ubuf[cur]), g, theta, pending ? pr : nullptr)));
@@ -1984,7 +1964,7 @@ static void clear_graphs(insb200_ctx *c) {
 template <typename T, int D>
 static int rk_step_graphed(insb200_ctx *c, const Tableau &tb, double dt, double theta) {
   const bool wanted = c->use_graphs > 0 || (c->use_graphs < 0 && c->cint <= ((i64)1 << 22));
-  const bool usable = wanted && c->nranks == 1 && !c->profiling && c->stream != nullptr && c->stream != cudaStreamLegacy &&
+  const bool usable = wanted && c->nranks == 1 && !c->profiling && !c->force_cb && c->stream != nullptr && c->stream != cudaStreamLegacy &&
                       c->stream != cudaStreamPerThread;
   if (!usable) return rk_step_compact<T, D>(c, tb, dt, theta);
   if (!c->graph_warm) {
@@ -2066,6 +2046,7 @@ static int op_rk_steps(insb200_ctx *c, void *u, double *t, double dt, int nsteps
   if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[0] = o[0]; }
   T tt = T(*t);
   for (int n = 0; n < nsteps; n++) {
+    c->t_step = (double)tt;
     INS_TRY((rk_step_graphed<T, D>(c, tb, dt, theta)));
     tt = tt + T(tb.c[tb.s - 1]) * T(dt);  // t = tstart + c[i]*dt (:32)
     if (ke_hist) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[n + 1] = o[0]; }
@@ -2099,6 +2080,7 @@ static int op_solve_host(insb200_ctx *c, void *u_host, double t0, double tend, d
     const T d = (te - t) / T((double)nstep);
     if (max_steps > 0 && nstep > max_steps) nstep = max_steps;
     for (; n < nstep; n++) {
+      c->t_step = (double)t;
       INS_TRY((rk_step_graphed<T, D>(c, tb, (double)d, theta)));
       t = t + T(tb.c[tb.s - 1]) * d;
       if (ke_hist && nk < ke_cap) { INS_TRY((reduce_compact<T, D>(c, o))); ke_hist[nk++] = o[0]; }
@@ -2113,6 +2095,7 @@ static int op_solve_host(insb200_ctx *c, void *u_host, double t0, double tend, d
         d = T(cfl) * T(cfl_from_max<T>(c, o));
       }
       d = std::min(d, te - t);
+      c->t_step = (double)t;
       INS_TRY((rk_step_compact<T, D>(c, tb, (double)d, theta)));
       t = t + T(tb.c[tb.s - 1]) * d;
       n++;

@@ -575,6 +575,7 @@ extern "C" int insb200_rk_step_temp(insb200_ctx *c, void *u, void *temp, double 
   TQ_PROLOG(c);
   if (!u || !temp) INS_FAIL(c, "NULL field");
   INS_TRY(need_temperature(c));
+  if (c->force_cb) INS_FAIL(c, "the temperature stepper takes steady body forces only (no unsteady-force callback)");
   INS_TRY(check_tableau(c, s, A, cc));
   double tt = t;
   return TQ_DISPATCH(c, op_rk_steps_temp, c, u, temp, &tt, dt, 1, s, A, cc, theta, p_out);
@@ -585,12 +586,14 @@ extern "C" int insb200_rk_steps_temp(insb200_ctx *c, void *u, void *temp, double
   if (!u || !temp || !t) INS_FAIL(c, "NULL argument");
   if (nsteps < 0) INS_FAIL(c, "nsteps < 0");
   INS_TRY(need_temperature(c));
+  if (c->force_cb) INS_FAIL(c, "the temperature stepper takes steady body forces only (no unsteady-force callback)");
   INS_TRY(check_tableau(c, s, A, cc));
   return TQ_DISPATCH(c, op_rk_steps_temp, c, u, temp, t, dt, nsteps, s, A, cc, theta, nullptr);
 }
 extern "C" int insb200_right_hand_side(insb200_ctx *c, void *dudt, const void *u, double t) {
   TQ_PROLOG(c);
   if (!dudt || !u) INS_FAIL(c, "NULL field");
+  if (c->force_cb) INS_FAIL(c, "right_hand_side! takes steady body forces only (no unsteady-force callback)");
   return TQ_DISPATCH(c, op_right_hand_side, c, dudt, u, t);
 }
 extern "C" int insb200_qfield(insb200_ctx *c, void *Q, const void *u) {

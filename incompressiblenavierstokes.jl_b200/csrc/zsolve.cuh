@@ -237,7 +237,10 @@ __device__ __forceinline__ void zsolve_tile(Cx<T> *s, const Cx<T> *tw, const T *
 }
 
 // S: spectrum, layout [z][ncols] (column index fastest: c = ky*nxw + kx_local).  nz = 2^m.
-template <typename T, int COLS>
+// TAG only names the instantiation: insb200.cu (built with -fmad=false: TAG 0, the `exact` mode) and fast.cu (FMA
+// contraction on: TAG 1, the default) both instantiate this template, and two kernels with one mangled name but
+// different code would collide when the library is linked.
+template <typename T, int COLS, int TAG = 0>
 __global__ void __launch_bounds__(512) k_zsolve(const __grid_constant__ CUtensorMap tm, const Cx<T> *__restrict__ twg,
                                                 const T *__restrict__ ax, const T *__restrict__ ay,
                                                 const T *__restrict__ az, int nz, long long ncols, int nxw, int kx0,
