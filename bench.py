@@ -11,6 +11,8 @@ Workloads (BASELINE.json configs):
              keeps 512^3 cells: N=2 512x512x1024, N=4 512x1024x1024, N=8 1024^3.
   tgv3d      TaylorGreenVortex3D periodic, Float32, no closure (config 5 is its 8-GPU 1024^3 case).
   kolmo2d    Kolmogorov2D forced periodic 4096^2 Float32 (config 3).
+  tgv3d_f64  TaylorGreenVortex3D periodic 128^3 Float64 (config 2).
+  dt2d_f64   DecayingTurbulence2D periodic 256^2 Float64 (config 1; the parity run is adaptive, the timed one uses dt = 1e-3).
 One JSON line on rank 0:
   value     Mcell-updates/s, state resident in HBM, K steps inside ONE insb200_rk_steps call
   e2e       the same metric through insb200_solve_unsteady_host: HOST buffer in, H2D, K steps with a
@@ -46,6 +48,8 @@ WORKLOADS = {
                   title="TaylorGreenVortex3D periodic 512^3/GPU Float32, RK44, psolver_spectral"),
     "tgv3d_f64": dict(D=3, n=128, T="float64", Re=1e3, dt=1e-3, theta=None, force=False,
                       title="TaylorGreenVortex3D periodic 128^3 Float64, RK44, psolver_spectral"),
+    "dt2d_f64": dict(D=2, n=256, T="float64", Re=4e3, dt=1e-3, theta=None, force=False,
+                     title="DecayingTurbulence2D periodic 256^2 Float64, RK44, psolver_spectral (fixed dt for timing)"),
     "kolmo2d": dict(D=2, n=4096, T="float32", Re=2e3, dt=2.5e-5, theta=None, force=True,
                     title="Kolmogorov2D forced periodic 4096^2/GPU Float32, RK44, psolver_spectral"),
 }
@@ -562,7 +566,7 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
         closure_fused = theta is not None and "smagorinsky_fused" not in timers and "smagtensor" not in timers
         words = kernel_words(D, theta is not None, wl["force"], tma=(D == 3 and base_n % 32 == 0),
                              zsolve=(D == 3 and 8 <= nz_glob <= 2048 and nz_glob & (nz_glob - 1) == 0),
-                             fused2d=(D == 2 and theta is None and "divergence" not in timers),
+                             fused2d=(D == 2 and theta is None and not any(kv.replace(" ", "") == "fuse2d=0" for kv in args.param)),
                              closure_fused=closure_fused)
         kern = {}
         for name, (tms, cnt) in timers.items():

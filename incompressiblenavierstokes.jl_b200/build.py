@@ -54,6 +54,8 @@ def needs_build():
 
 
 def build(force=False, verbose=False, extra_flags=()):
+    """extra_flags=("-DINSB200_EXPERIMENTAL",) also compiles the recorded negative results (packed-FP32 stage kernel
+    k_stage3d_tma_x2, fused peer z-solve k_zsolve_peer); the shipped library leaves them out."""
     if not force and not needs_build():
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)

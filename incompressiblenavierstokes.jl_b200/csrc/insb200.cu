@@ -11,7 +11,9 @@
 #include "stencil.cuh"
 #include "tiled.cuh"
 #include "tma_stage.cuh"
+#ifdef INSB200_EXPERIMENTAL  // negative results kept for reference: packed-FP32 stage kernel, fused peer z-solve
 #include "tma_stage_x2.cuh"
+#endif
 #include "stage2d.cuh"
 #include "zsolve.cuh"
 #include "zsolve_launch.cuh"
@@ -1597,6 +1599,7 @@ static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T
   INS_TRY(get_tmap(c, pbase, 1, Cfg::Pipe::BX, kTY + 4, &tp));
   const int zc = auto_zchunk(c, c->zchunk, (c->nloc[0] / kTX) * (c->nloc[1] / kTY), sizeof(T) == 4 ? 2 : 1, 4);
   dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
+#ifdef INSB200_EXPERIMENTAL
   if constexpr (std::is_same<T, float>::value) if (c->stage_x2) {  // two cells per thread on packed FP32 (tma_stage_x2.cuh)
     auto kex = k_stage3d_tma_x2<f2t<true>, PG, SA, GEN, kTX, kTY, kNS>;    // 1: exact (bit-identical to the scalar kernel)
     auto kfu = k_stage3d_tma_x2<f2t<false>, PG, SA, GEN, kTX, kTY, kNS>;   // 2: products contracted into FFMA2
@@ -1611,6 +1614,7 @@ static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T
     CHECK_LAUNCH(c);
     return 0;
   }
+#endif
   auto kern = k_stage3d_tma<T, PG, SA, GEN, kTX, kTY, kNS>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -1836,10 +1840,10 @@ static int rk_step_tma(insb200_ctx *c, const Tableau &tb, double dt, double thet
   return 0;
 }
 
-// fused 2-D stage kernel (stage2d.cuh): one rank, periodic by index wrap, rows of at least 3 cells
+// fused 2-D stage kernel (stage2d.cuh): rows wrap by index on one rank, ghost rows on slabs; rows of at least 3 cells
 template <typename T, int D>
 static bool fused2d_supported(const insb200_ctx *c) {
-  return D == 2 && c->nranks == 1 && c->fuse2d && c->nloc[0] >= 4 && c->nloc[1] >= 4;
+  return D == 2 && c->fuse2d && c->nloc[0] >= 4 && c->nloc[1] >= 4;
 }
 template <typename T>
 static int launch_stage2d(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, Rh<T> rh) {
@@ -1882,7 +1886,7 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
     const int nxt = (cur == 1) ? 2 : 1;
     if (c->force_cb) INS_TRY((update_unsteady_force<T, D>(c, stage_time<T>(c, tb.c, i, dt))));
     // apply_bc_u! before momentum (step_explicit_runge_kutta.jl:19): wrap by index, halos over NCCL
-    if (!pending) INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, 1, 1)));  // (pending: exchanged after the stage kernel)
+    if (!pending) INS_TRY((halo_compact<T>(c, c->ubuf[cur], D, f2d ? 2 : 1, 1)));  // (pending: exchanged after the stage kernel)
     if (smag) INS_TRY((compute_sigma<T, D>(c, view_compact_c<T>(c, c->ubuf[cur]), g, theta, pending ? pr : nullptr)));
     StageArgs<T> a;
     memset(&a, 0, sizeof a);
@@ -1918,13 +1922,19 @@ static int rk_step_compact(insb200_ctx *c, const Tableau &tb, double dt, double 
         if constexpr (D == 2) INS_TRY((launch_stage2d<T>(c, a, g, visc, rh)));  // f2d (tiled implies it in 2-D)
         else INS_TRY((launch_stage_tiled<T, D>(c, a, g, visc, rh, smag)));
       }
-      // u' halos: the minus side for the chunk-first planes of the divergence, both for the next stage
-      INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, 1, 1)));
+      // u' halos: the minus side for the chunk-first planes of the divergence, both for the next stage (the fused 2-D
+      // kernel reads two rows below its first one)
+      INS_TRY((halo_compact<T>(c, c->ubuf[nxt], D, f2d ? 2 : 1, 1)));
       if constexpr (D == 3) INS_TRY((launch_divergence_planes<T>(c, pr, (const T *)c->ubuf[nxt] + goff, g)));
+      if constexpr (D == 2) if (c->nranks > 1) {
+        ScopedTimer tm(c, TM_DIVERGENCE);
+        k_divergence_row0<T><<<(c->nloc[0] + 255) / 256, 256, 0, c->stream>>>(pr, (const T *)c->ubuf[nxt] + goff, c->csy, c->ccomp, c->nloc[0], rh, volume<T>(c));
+        CHECK_LAUNCH(c);
+      }
       INS_TRY((poisson_solve<T, D>(c)));
       const bool last = i == tb.s - 1;
       if (fuse_grad && !last) {
-        INS_TRY((halo_compact<T>(c, c->preal, 1, 1, 2)));
+        INS_TRY((halo_compact<T>(c, c->preal, 1, f2d ? 2 : 1, 2)));
         pending = true;
       } else {
         INS_TRY((halo_compact<T>(c, c->preal, 1, 0, 1)));
@@ -2220,7 +2230,14 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "rows2d") c->rows2d = v != 0;
   else if (k == "fuse2d") c->fuse2d = v != 0;
   else if (k == "rows_chunk") { if (v != 0 && v < 2) INS_FAIL(c, "rows_chunk must be 0 (automatic) or >= 2"); c->rows_chunk = v; }
-  else if (k == "stage_x2") { if (v < 0 || v > 2) INS_FAIL(c, "stage_x2 must be 0, 1 or 2"); c->stage_x2 = v; }
+  else if (k == "stage_x2") {
+#ifdef INSB200_EXPERIMENTAL
+    if (v < 0 || v > 2) INS_FAIL(c, "stage_x2 must be 0, 1 or 2");
+    c->stage_x2 = v;
+#else
+    if (v != 0) INS_FAIL(c, "stage_x2: the packed-FP32 stage kernel is a negative result kept behind -DINSB200_EXPERIMENTAL (DESIGN.md section 4)");
+#endif
+  }
   else if (k == "smag_v") { if (v != 1 && v != 2) INS_FAIL(c, "smag_v must be 1 or 2"); c->smag_v = v; }
   else if (k == "fft_pipe") {
     if (c->plans) INS_FAIL(c, "fft_pipe must be set before the first pressure solve");

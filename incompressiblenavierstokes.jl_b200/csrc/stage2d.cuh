@@ -1,4 +1,7 @@
-// stage2d.cuh -- fused RK stage kernel of the 2-D path (compact layout, one rank): what k_stage3d_tma is to 3-D.
+// stage2d.cuh -- fused RK stage kernel of the 2-D path (compact layout): what k_stage3d_tma is to 3-D.  One rank: rows
+// wrap by index; slabs (nranks > 1, g.wrap[1] == 0): the two ghost rows on each side of the slab are read instead
+// (u: 2 below / 1 above, p: 2 / 2) and the divergence of the slab's FIRST row -- which needs u'_y of the neighbour rank's
+// last row -- is completed by k_divergence_row0 after the halo exchange of u'.
 //
 // One launch per stage does   [u = u' - grad p of the previous stage, on load]  ->  k_i = momentum!(u) [+ force]  ->
 // u' = ustart + sum_j (dt a_ij) k_j  ->  div = divergence!(u') * Omega   (step_explicit_runge_kutta.jl:17-50 up to the
@@ -53,14 +56,16 @@ __global__ void __launch_bounds__(32 * kS2Warps)
   const bool store = lane >= 2 && lane <= 30 && col < n0;
   const bool need = lane >= 1 && lane <= 30;   // lanes whose u' enters a stored value
   const int jbeg = blockIdx.y * rc, jend = min(jbeg + rc, n1);
+  const int wy = g.wrap[1];                     // 0: ghost rows are addressable (slab of a decomposed grid)
+  const bool have_prev = jbeg > 0 || wy != 0;   // otherwise row 0's divergence is completed by k_divergence_row0
   const i64 sy = A.sy, sc = A.sc;
   const bool u0_is_u = A.u0 == A.u;
 
   // raw row r of the stage input: u' (and p for the projection)
-  auto row = [&](int r) -> i64 { return (i64)wrapi(r, n1, 1) * sy + cw; };
+  auto row = [&](int r) -> i64 { return (i64)wrapi(r, n1, wy) * sy + cw; };
   T pn = T(0);  // p(col, r) of the next row to bring in (carried: the upper p of one row is the lower p of the next)
   auto load_p = [&](int r) -> T { return PGRAD ? __ldg(A.pin + row(r)) : T(0); };
-  auto load_pe = [&](int r) -> T { return (PGRAD && lane == 31) ? __ldg(A.pin + (i64)wrapi(r, n1, 1) * sy + cwp) : T(0); };
+  auto load_pe = [&](int r) -> T { return (PGRAD && lane == 31) ? __ldg(A.pin + (i64)wrapi(r, n1, wy) * sy + cwp) : T(0); };
   // projected row from raw values: u_x - (p(+1,0) - p) / h_x,  u_y - (p(0,+1) - p) / h_y   (operators.jl:225-233)
   auto project = [&](T &ux, T &uy, T p0, T p1, T pe) {
     if (!PGRAD) return;
@@ -155,7 +160,7 @@ __global__ void __launch_bounds__(32 * kS2Warps)
       }
     }
     const T unx_m = __shfl_up_sync(FULL, un[0], 1);
-    if (store && !pre) {
+    if (store && !pre && (j > jbeg || have_prev)) {
       T d = T(0);
       d += (un[0] - unx_m) * rh.v[0];
       d += (un[1] - uy_prev) * rh.v[1];
@@ -163,6 +168,19 @@ __global__ void __launch_bounds__(32 * kS2Warps)
     }
     uy_prev = un[1];
   }
+}
+
+// divergence(u') * Omega on row 0 of a slab (2-D, nranks > 1): the fused kernel cannot form u'_y of the neighbour rank's
+// last row; after the halo exchange it sits in ghost row -1 (operators.jl:106-125, 81-95, same expression order)
+template <typename T>
+__global__ void k_divergence_row0(T *__restrict__ out, const T *__restrict__ u, i64 sy, i64 sc, int n0, Rh<T> rh, T vol) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n0) return;
+  const int im = i == 0 ? n0 - 1 : i - 1;
+  T d = T(0);
+  d += (u[i] - u[im]) * rh.v[0];
+  d += (u[sc + i] - u[sc + i - sy]) * rh.v[1];
+  out[i] = d * vol;
 }
 
 }  // namespace insb200

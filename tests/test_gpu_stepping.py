@@ -224,16 +224,10 @@ def test_kernel_variants_bit_identical(T, smag):
                          ("tiled16", dict(variant=1, tile_y=16, zchunk=64, fuse_gradient=1)),
                          ("tiled8_zc16", dict(variant=1, tile_y=8, zchunk=16, fuse_gradient=1)),
                          ("tiled16_zc7_nofuse", dict(variant=1, tile_y=16, zchunk=7, fuse_gradient=0)),
-                         ("tma_zc64", dict(variant=2, zchunk=64, stage_x2=0)),
+                         ("tma_zc64", dict(variant=2, zchunk=64)),
                          ("tma_zc7", dict(variant=2, zchunk=7)),
                          ("tma_zc2", dict(variant=2, zchunk=2)),
-                         # two cells per thread on packed FP32 (Float32 only; exact = scalar multiplies, packed adds)
-                         ("tma_x2_zc64", dict(variant=2, zchunk=64, stage_x2=1)),
-                         ("tma_x2_zc7", dict(variant=2, zchunk=7)),
-                         ("tma_x2_zc2", dict(variant=2, zchunk=2)),
-                         ("tma_x2fused_zc64", dict(variant=2, zchunk=64, stage_x2=2)),
-                         ("tma_x2fused_zc5", dict(variant=2, zchunk=5)),
-                         ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1, stage_x2=1)),
+                         ("tma_smag_v1", dict(variant=2, zchunk=64, smag_v=1)),
                          ("tma_smag_v2_zc128", dict(variant=2, smag_v=2, smag_zchunk=128)),
                          ("tma_smag_v2_zc7", dict(variant=2, smag_v=2, smag_zchunk=7)),
                          ("tma_smag_v2_zc2", dict(variant=2, smag_v=2, smag_zchunk=2)),
