@@ -55,7 +55,8 @@ def needs_build():
 
 def build(force=False, verbose=False, extra_flags=()):
     """extra_flags=("-DINSB200_EXPERIMENTAL",) also compiles the recorded negative results (packed-FP32 stage kernel
-    k_stage3d_tma_x2, fused peer z-solve k_zsolve_peer); the shipped library leaves them out."""
+    k_stage3d_tma_x2, fused peer z-solve k_zsolve_peer); the shipped library leaves them out.  extra_flags=("-DINSB200_DEBUG",)
+    bounds every mbarrier wait and traps with a message instead of hanging (tma_stage.cuh)."""
     if not force and not needs_build():
         return LIB
     os.makedirs(LIBDIR, exist_ok=True)

@@ -130,6 +130,25 @@ __global__ void __launch_bounds__(32 * kSc2Warps)
   }
 }
 
+// Local unpack of the packed transposes (transpose_mode 2): R[src][row][k] (k < w_src, blocks of rows * w_src words at
+// offset rows * src * kxc -- what the peers' contiguous copies left in this rank's staging buffer) -> S[row][src kxc + k].
+// The local PACK is k_fft_scatter2_fwd itself with all destination pointers aimed at the local staging buffer.
+template <typename C>
+__global__ void __launch_bounds__(32 * kSc2Warps)
+    k_fft_unpack(C *__restrict__ S, const C *__restrict__ R, int nxh, int ps, i64 rows, int kxc, int nranks, i64 rbeg, i64 rend) {
+  const i64 ngroups = (rend - rbeg + kSc2Rows - 1) / kSc2Rows, nitems = ngroups * nranks;
+  const i64 nwarps = (i64)gridDim.x * kSc2Warps;
+  for (i64 it = (i64)blockIdx.x * kSc2Warps + threadIdx.y; it < nitems; it += nwarps) {
+    const i64 g = it / nranks;
+    const int src = (int)(it - g * nranks);
+    const int w = src == nranks - 1 ? nxh - src * kxc : kxc;
+    if (w <= 0) continue;
+    const i64 r0 = rbeg + g * kSc2Rows;
+    const int nr = (int)(rend - r0 < kSc2Rows ? rend - r0 : kSc2Rows);
+    copy_rows<C>(S + r0 * ps + (i64)src * kxc, ps, R + rows * (i64)src * kxc + r0 * w, w, w, nr, threadIdx.x);
+  }
+}
+
 // ---- halo planes --------------------------------------------------------------------------------------------------
 // Planes of a compact / padded buffer (nc components of stride sc, plane size pl elements, G ghost planes below the
 // nl interior planes): the top wminus interior planes go into the NEXT rank's lower ghost planes, the bottom wplus

@@ -87,7 +87,7 @@ struct insb200_ctx {
                            // one chunk overlaps the cuFFT of the next on a second stream (1 = no pipelining)
   int fft_pipe_min_ranks = 2;
   cudaStream_t comm_stream = nullptr;
-  cudaEvent_t pipe_ev[16] = {nullptr}, pipe_sync = nullptr;
+  cudaEvent_t pipe_ev[16] = {nullptr}, pack_ev[16] = {nullptr}, pipe_sync = nullptr;
   int fft_chunk = 0;       // param: planes per in-plane cuFFT exec (0 = the whole slab); small chunks keep the x->y intermediate in L2
   int fft_batch = 0;       // planes per exec of plan_fwd_in / plan_inv_in as planned
   long long fft_cdist = 0; // complex words between consecutive planes of the in-slab spectrum
@@ -149,6 +149,8 @@ struct insb200_ctx {
   void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter (NCCL fallback)
   void *flagbuf = nullptr, *peerF[16] = {nullptr};      // barrier flag words of this rank / of every rank (CUDA IPC): k_peer_barrier
   unsigned bar_epoch = 0;                               // barriers issued so far (same sequence on every rank)
+  int transpose_mode = 2;                               // param "transpose_mode" (pipelined path): 2 = local pack -> CONTIGUOUS peer copies on the copy engines -> local unpack; 1 = pitched peer copies (transpose_ce); 0 = scatter kernels
+  void *pstage = nullptr, *peerP[16] = {nullptr};       // staging buffer of the packed transposes (own / every rank's, CUDA IPC)
   int transpose_ce = 1;                                 // param "transpose_ce": 1 = transposes as pitched peer copies on the copy engines, 0 = scatter kernels
   std::vector<cudaStream_t> ce_streams;                 // one stream per destination slot of the copy-engine transposes
   std::vector<cudaEvent_t> ce_events;                   // [chunk][destination slot]

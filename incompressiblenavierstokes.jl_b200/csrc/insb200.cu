@@ -315,6 +315,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
       if (q != c->rank && c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
       if (q != c->rank && c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
       if (q != c->rank && c->peerF[q]) cudaIpcCloseMemHandle(c->peerF[q]);
+      if (q != c->rank && c->peerP[q]) cudaIpcCloseMemHandle(c->peerP[q]);
     }
   }
   for (auto &kv : c->halo_peers) {
@@ -324,11 +325,13 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   if (c->comm_stream) {
     cudaStreamSynchronize(c->comm_stream);
     for (auto &e : c->pipe_ev) if (e) cudaEventDestroy(e);
+    for (auto &e : c->pack_ev) if (e) cudaEventDestroy(e);
     if (c->pipe_sync) cudaEventDestroy(c->pipe_sync);
     cudaStreamDestroy(c->comm_stream);
   }
   if (c->barbuf) cudaFree(c->barbuf);
   if (c->flagbuf) cudaFree(c->flagbuf);
+  if (c->pstage) cudaFree(c->pstage);
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
@@ -382,8 +385,9 @@ static void close_p2p(insb200_ctx *c) {
       if (c->peerS[q]) cudaIpcCloseMemHandle(c->peerS[q]);
       if (c->peerB[q]) cudaIpcCloseMemHandle(c->peerB[q]);
       if (c->peerF[q]) cudaIpcCloseMemHandle(c->peerF[q]);
+      if (c->peerP[q]) cudaIpcCloseMemHandle(c->peerP[q]);
     }
-    c->peerS[q] = c->peerB[q] = c->peerF[q] = nullptr;
+    c->peerS[q] = c->peerB[q] = c->peerF[q] = c->peerP[q] = nullptr;
   }
   c->p2p = 0;
 }
@@ -394,8 +398,8 @@ static void close_p2p(insb200_ctx *c) {
 static int setup_p2p(insb200_ctx *c) {
   if (!c->p2p_enable || c->nranks > 16) return 0;
   struct Rec {
-    cudaIpcMemHandle_t h[3];
-    int ok, pad[15];
+    cudaIpcMemHandle_t h[4];
+    int ok, has_stage, pad[14];
   };
   INS_TRY(dev_alloc(c, &c->barbuf, 256));
   INS_TRY(dev_alloc(c, &c->flagbuf, (size_t)2 << 20));  // zeroed: epochs start at 1.  2 MiB: an allocation of its own (IPC maps whole allocations)
@@ -405,6 +409,8 @@ static int setup_p2p(insb200_ctx *c) {
   memset(&mine, 0, sizeof(mine));
   mine.ok = cudaIpcGetMemHandle(&mine.h[0], c->pcplx) == cudaSuccess && cudaIpcGetMemHandle(&mine.h[1], c->pcplx2) == cudaSuccess &&
             cudaIpcGetMemHandle(&mine.h[2], c->flagbuf) == cudaSuccess;
+  mine.has_stage = c->pstage != nullptr;
+  if (mine.ok && c->pstage) mine.ok = cudaIpcGetMemHandle(&mine.h[3], c->pstage) == cudaSuccess;
   if (!mine.ok) cudaGetLastError();
   void *dev = nullptr;
   INS_CUDA(c, cudaMalloc(&dev, sizeof(Rec) * c->nranks));
@@ -416,7 +422,8 @@ static int setup_p2p(insb200_ctx *c) {
   for (int q = 0; q < c->nranks; q++) ok &= all[q].ok;
   if (ok) {
     for (int q = 0; q < c->nranks && ok; q++) {
-      if (q == c->rank) { c->peerS[q] = c->pcplx; c->peerB[q] = c->pcplx2; c->peerF[q] = c->flagbuf; continue; }
+      if (q == c->rank) { c->peerS[q] = c->pcplx; c->peerB[q] = c->pcplx2; c->peerF[q] = c->flagbuf; c->peerP[q] = c->pstage; continue; }
+      if (c->pstage && all[q].has_stage && cudaIpcOpenMemHandle(&c->peerP[q], all[q].h[3], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerP[q] = nullptr; ok = 0; }
       if (cudaIpcOpenMemHandle(&c->peerS[q], all[q].h[0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerS[q] = nullptr; ok = 0; }
       else if (cudaIpcOpenMemHandle(&c->peerB[q], all[q].h[1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerB[q] = nullptr; ok = 0; }
       else if (cudaIpcOpenMemHandle(&c->peerF[q], all[q].h[2], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->peerF[q] = nullptr; ok = 0; }
@@ -522,11 +529,14 @@ static int ensure_fft(insb200_ctx *c) {
     // rows of the in-slab spectrum: 3-D: ny*nzl, 2-D: nyl
     const i64 rows = D == 3 ? (i64)c->nloc[1] * c->nloc[2] : c->nloc[1];
     // row pitch of the in-slab spectrum: a multiple of 16 B so that the peers can address it by TMA
-    if (D == 3 && f32) c->nxp = (c->nxh + 1) & ~1;
+    // row pitch of the in-slab spectrum: a multiple of 128 B, so that the row pieces the transposes read and write
+    // (64 complex words = 512 B at 1024^3 on 8 ranks) start on 128-byte lines
+    if (D == 3) c->nxp = (c->nxh + (f32 ? 15 : 7)) & ~(f32 ? 15 : 7);
     const i64 kxmax = c->nxh - (i64)(c->nranks - 1) * c->kxc;                 // the last rank's (largest) column count
     const i64 slots = std::max((i64)c->nranks * kxmax, (i64)c->nxp) * rows;   // >= rows*nxp and >= nranks*rows*kxl
     INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
     INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
+    if (D == 3 && c->p2p_enable && c->transpose_mode == 2) INS_TRY(dev_alloc(c, &c->pstage, (size_t)slots * 2 * es));
     if (D == 3) {
       int nn[2] = {c->nloc[1], c->nloc[0]};
       int remb[2] = {c->ext[1], c->ext[0]};
@@ -864,6 +874,10 @@ static int poisson_solve(insb200_ctx *c) {
     const i64 need = ((nr + kSc2Rows - 1) / kSc2Rows * P + kSc2Warps - 1) / kSc2Warps;
     return dim3((unsigned)std::max<i64>(1, std::min<i64>(need, c->scatter_blocks)), 1, 1);
   };
+  auto lgrid = [&](i64 nr) {  // the same kernels moving LOCAL memory (pack / unpack of the packed transposes): fill the machine
+    const i64 need = ((nr + kSc2Rows - 1) / kSc2Rows * P + kSc2Warps - 1) / kSc2Warps;
+    return dim3((unsigned)std::max<i64>(1, std::min<i64>(need, 8 * (i64)c->nsm)), 1, 1);
+  };
   const bool pipelined = c->p2p && D == 3 && zsolve_supported(c) && c->fft_batch > 0 && c->nloc[2] % c->fft_batch == 0;
   C *W = c->p2p ? B : S;  // the transposed spectrum (kxl fastest, ky, global z) of this rank
   PeerPtrs pS, pB;
@@ -881,9 +895,20 @@ static int poisson_solve(insb200_ctx *c) {
     if (!c->comm_stream) {
       INS_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
       for (int b = 0; b < 16; b++) INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_ev[b], cudaEventDisableTiming));
+      for (int b = 0; b < 16; b++) INS_CUDA(c, cudaEventCreateWithFlags(&c->pack_ev[b], cudaEventDisableTiming));
       INS_CUDA(c, cudaEventCreateWithFlags(&c->pipe_sync, cudaEventDisableTiming));
     }
-    const bool ce = c->transpose_ce != 0;
+    // transpose_mode 2 (default): local pack (SM kernel at HBM speed) -> one CONTIGUOUS peer copy per destination on the
+    // copy engines -> local unpack on the receiving side after the barrier.  8 GPUs, 1024^3: the direct forms move
+    // 512-byte row pieces and reach 290 (pitched copies) / 360 GB/s (scatter kernels) per GPU; contiguous peer copies
+    // run at the copy engines' full rate (profiles/r2_sweep_*8gpu*).
+    const bool packed = c->transpose_mode == 2 && c->pstage != nullptr;
+    for (int q = 0; packed && q < P; q++) if (!c->peerP[q]) INS_FAIL(c, "packed transposes: a peer's staging buffer is not mapped");
+    const bool ce = packed || c->transpose_ce != 0;
+    C *PS = (C *)c->pstage;
+    PeerPtrs pPack;  // local pack = k_fft_scatter2_fwd with every destination aimed at this rank's staging buffer
+    for (int q = 0; q < 16; q++) pPack.p[q] = nullptr;
+    for (int q = 0; packed && q < P; q++) pPack.p[q] = (void *)(PS + rows * (i64)q * c->kxc - (i64)c->rank * rows * chunk_w(q));
     if (ce && c->ce_streams.empty()) {
       c->ce_streams.resize(P);
       for (int d = 0; d < P; d++) INS_CUDA(c, cudaStreamCreateWithFlags(&c->ce_streams[d], cudaStreamNonBlocking));
@@ -896,6 +921,32 @@ static int poisson_solve(insb200_ctx *c) {
       INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, after, 0));
       ScopedTimer ts(c, TM_SCATTER, c->comm_stream);
       const i64 r0 = b * rb;
+      if (packed) {
+        cudaEvent_t start = after;
+        if (fwd) {  // pack chunk b: S (strided rows) -> staging, one contiguous block per destination
+          k_fft_scatter2_fwd<C><<<lgrid(rb), sblk, 0, c->comm_stream>>>(pPack, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, r0, r0 + rb);
+          CHECK_LAUNCH(c);
+          start = c->pack_ev[b];
+          INS_CUDA(c, cudaEventRecord(start, c->comm_stream));
+        }
+        for (int d = 0; d < P; d++) {
+          const int q = (d + c->rank + 1) % P;  // every rank starts with a different peer
+          const int w = fwd ? chunk_w(q) : c->kxl;
+          if (w <= 0) continue;
+          cudaStream_t st = c->ce_streams[d];
+          INS_CUDA(c, cudaStreamWaitEvent(st, start, 0));
+          if (fwd)  // my block for q -> q's transposed spectrum W_q[(rank * rows + r0)][.]
+            INS_CUDA(c, cudaMemcpyAsync((C *)c->peerB[q] + ((i64)c->rank * rows + r0) * w, PS + rows * (i64)q * c->kxc + r0 * w,
+                                        (size_t)rb * w * sizeof(C), cudaMemcpyDeviceToDevice, st));
+          else      // my solved block for q's slab -> q's staging R_q[rank][r0 ..][.]
+            INS_CUDA(c, cudaMemcpyAsync((C *)c->peerP[q] + rows * (i64)c->kx0 + r0 * w, B + ((i64)q * rows + r0) * w,
+                                        (size_t)rb * w * sizeof(C), cudaMemcpyDeviceToDevice, st));
+          cudaEvent_t ev = c->ce_events[(size_t)b * P + d];
+          INS_CUDA(c, cudaEventRecord(ev, st));
+          INS_CUDA(c, cudaStreamWaitEvent(c->comm_stream, ev, 0));
+        }
+        return 0;
+      }
       if (!ce) {
         if (fwd) k_fft_scatter2_fwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pB, S, c->nxh, c->nxp, rows, c->kxc, c->rank, P, r0, r0 + rb);
         else if (c->kxl > 0) k_fft_scatter2_bwd<C><<<sgrid(rb), sblk, 0, c->comm_stream>>>(pS, B, c->nxp, rows, c->kxl, c->kx0, c->rank, P, r0, r0 + rb);
@@ -949,6 +1000,10 @@ static int poisson_solve(insb200_ctx *c) {
       for (int b = 0; b < NB; b++) {
         INS_CUDA(c, cudaStreamWaitEvent(c->stream, c->pipe_ev[b], 0));
         INS_TRY(peer_barrier(c));  // chunk b of every rank's spectrum is complete
+        if (packed) {              // ... in the staging buffer: unpack it into the in-slab spectrum
+          k_fft_unpack<C><<<lgrid(rb), sblk, 0, c->stream>>>(S, PS, c->nxh, c->nxp, rows, c->kxc, P, b * rb, (b + 1) * rb);
+          CHECK_LAUNCH(c);
+        }
         T *r = pr + (i64)b * c->fft_batch * c->csz;
         C *s = S + (i64)b * c->fft_batch * c->fft_cdist;
         if (sizeof(T) == 4) INS_CUFFT(c, cufftExecC2R(c->plan_inv_in, (cufftComplex *)s, (cufftReal *)r));
@@ -2254,6 +2309,12 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
   else if (k == "p2p_halo") c->p2p_halo = v != 0;
   else if (k == "fast_barrier") c->fast_barrier = v != 0;
   else if (k == "transpose_ce") c->transpose_ce = v != 0;
+  else if (k == "transpose_mode") {
+    if (v < 0 || v > 2) INS_FAIL(c, "transpose_mode must be 0 (scatter kernels), 1 (pitched peer copies) or 2 (pack + contiguous peer copies)");
+    if (c->plans && c->nranks > 1 && v == 2 && !c->pstage) INS_FAIL(c, "transpose_mode 2 must be set before the first pressure solve");
+    c->transpose_mode = v;
+    if (v < 2) c->transpose_ce = v;
+  }
   else if (k == "scatter_blocks") { if (v < 1 || v > 65535) INS_FAIL(c, "scatter_blocks must be in [1, 65535]"); c->scatter_blocks = v; }
   else if (k == "p2p_fused") { if (v != 0) INS_FAIL(c, "p2p_fused: the fused peer transposes (k_zsolve_peer) are a negative result kept behind -DINSB200_EXPERIMENTAL (DESIGN.md)"); }
   else if (k == "p2p") {

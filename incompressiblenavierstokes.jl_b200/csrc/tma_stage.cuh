@@ -34,7 +34,30 @@ __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// Wait for phase `parity` of an mbarrier.  try_wait suspends the thread for a hardware-chosen time slice before it
+// returns false, so the loop is not a hot spin.  -DINSB200_DEBUG bounds it: a wrong expect_tx byte count (the classic
+// TMA bug) traps after about a second with the barrier's address instead of hanging the SM until the watchdog fires.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#ifdef INSB200_DEBUG
+  const long long t0 = clock64();
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, P1;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!done && clock64() - t0 > 2000000000LL) {
+      printf("insb200: mbarrier %p (block %d,%d,%d thread %d) never completed phase %u -- wrong expect_tx?\n", (void *)bar, blockIdx.x,
+             blockIdx.y, blockIdx.z, threadIdx.x + threadIdx.y * blockDim.x, parity);
+      __trap();
+    }
+  }
+#else
   asm volatile(
       "{\n"
       ".reg .pred P1;\n"
@@ -46,6 +69,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       "}\n" ::"r"(smem_u32(bar)),
       "r"(parity)
       : "memory");
+#endif
 }
 __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *tm, uint64_t *bar, int x, int y, int z, int c) {
   asm volatile(

@@ -25,6 +25,7 @@ CASES = [
     ((32, 16, 32), np.float32, True, 0.17, 4, 1e-3),         # TMA path + closure + force
     ((24, 20, 16), np.float64, False, 0.17, 3, 2e-3),        # generic path (not tile aligned)
     ((64, 32, 64), np.float32, False, 0.17, 2, 1e-3),        # 8 planes per rank at 8 GPUs, closure kernel v2
+    ((96, 64), np.float32, True, None, 6, 5e-4),             # 2-D Float32 + Kolmogorov force: fused 2-D stage kernel on slabs
 ]
 
 
@@ -54,9 +55,10 @@ def big_case(backend):
     sc = ins.Setup(xb, Re=T(2000), backend=backend)
     so.closure_model = o.smagorinsky_closure(so)
     sc.closure_model = ins.smagorinsky_closure(sc)
-    for k in ("MGPU_P2P", "MGPU_FASTBAR", "MGPU_EXACT"):
+    for k in ("MGPU_P2P", "MGPU_FASTBAR", "MGPU_EXACT", "MGPU_TMODE"):
         if k in os.environ:
-            sc.ctx.call("insb200_set_param", {"MGPU_P2P": b"p2p", "MGPU_FASTBAR": b"fast_barrier", "MGPU_EXACT": b"exact"}[k], float(os.environ[k]))
+            sc.ctx.call("insb200_set_param", {"MGPU_P2P": b"p2p", "MGPU_FASTBAR": b"fast_barrier", "MGPU_EXACT": b"exact",
+                                              "MGPU_TMODE": b"transpose_mode"}[k], float(os.environ[k]))
     u0 = o.random_field(so, kp=4, rng=np.random.default_rng(3))
     ul = ins.to_device(ins.local_slab(tile_box(u0, reps, 3), 3, rank, world), sc)
     m = ins.RKMethods.RK44(T=T)
@@ -107,6 +109,8 @@ def main():
             sc.ctx.call("insb200_set_param", b"fast_barrier", float(os.environ["MGPU_FASTBAR"]))
         if "MGPU_EXACT" in os.environ:  # 1 = the bit-exact kernels instead of k_stage3d_fast
             sc.ctx.call("insb200_set_param", b"exact", float(os.environ["MGPU_EXACT"]))
+        if "MGPU_TMODE" in os.environ:  # transposes: 2 = pack + contiguous peer copies (default), 1 = pitched peer copies, 0 = scatter kernels
+            sc.ctx.call("insb200_set_param", b"transpose_mode", float(os.environ["MGPU_TMODE"]))
         sc.ctx.call("insb200_set_param", b"fft_pipe_min_ranks", 2.0)  # exercise the pipelined transposes at any world size
         if theta is not None:
             so.closure_model = o.smagorinsky_closure(so)

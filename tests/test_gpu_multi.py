@@ -3,7 +3,7 @@ the box (skipped when fewer are visible).  Every rank owns one slab of the last 
 its peer-memory transposes and the all-reduced reductions are compared with the single-domain oracle on identical
 initial arrays -- small grids (2-D, TMA path, generic path, closure) and 256 x 256 x 512 Float32 + Smagorinsky against
 the tiled 64^3 oracle run.  Variants: peer-memory transposes with flag barriers (default), ncclAllReduce barriers,
-NCCL send/recv transposes, the bit-exact kernels."""
+the other two transpose forms (pitched peer copies, scatter kernels), NCCL send/recv transposes, the bit-exact kernels."""
 import os
 import socket
 import subprocess
@@ -24,14 +24,14 @@ def _free_port():
 
 
 @pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("variant", ["default", "nccl_barrier", "nccl_sendrecv", "exact"])
+@pytest.mark.parametrize("variant", ["default", "pitched_copies", "scatter_kernels", "nccl_barrier", "nccl_sendrecv", "exact"])
 def test_slab_path_matches_oracle(world, variant):
     import torch
 
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs, {torch.cuda.device_count()} visible")
-    env = dict(os.environ, **{"default": {}, "nccl_barrier": {"MGPU_FASTBAR": "0"}, "nccl_sendrecv": {"MGPU_P2P": "0"},
-                             "exact": {"MGPU_EXACT": "1"}}[variant])
+    env = dict(os.environ, **{"default": {}, "pitched_copies": {"MGPU_TMODE": "1"}, "scatter_kernels": {"MGPU_TMODE": "0"},
+                             "nccl_barrier": {"MGPU_FASTBAR": "0"}, "nccl_sendrecv": {"MGPU_P2P": "0"}, "exact": {"MGPU_EXACT": "1"}}[variant])
     if variant != "default":
         env["MGPU_BIG"] = "0" if variant == "nccl_sendrecv" else "1"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
