@@ -29,6 +29,7 @@ import os
 # The caller's NCCL_DEBUG / NCCL_DEBUG_FILE are honoured (the driver reads the communicator sizes from NCCL's INFO
 # log); only when nothing is set NCCL is kept quiet so that stdout carries the ONE JSON line and nothing else.
 os.environ.setdefault("NCCL_DEBUG", "WARN")
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # NCCL logs to stdout by default: keep them, but on stderr
 import subprocess
 import sys
 import threading

@@ -149,6 +149,7 @@ struct insb200_ctx {
   void *barbuf = nullptr;                               // one int: all-reduced as the barrier after a scatter (NCCL fallback)
   void *flagbuf = nullptr, *peerF[16] = {nullptr};      // barrier flag words of this rank / of every rank (CUDA IPC): k_peer_barrier
   unsigned bar_epoch = 0;                               // barriers issued so far (same sequence on every rank)
+  int transpose_mode_req = -1;                          // as set by the caller; -1 = automatic: by the size of the row pieces (ensure_fft)
   int transpose_mode = 2;                               // param "transpose_mode" (pipelined path): 2 = local pack -> CONTIGUOUS peer copies on the copy engines -> local unpack; 1 = pitched peer copies (transpose_ce); 0 = scatter kernels
   void *pstage = nullptr, *peerP[16] = {nullptr};       // staging buffer of the packed transposes (own / every rank's, CUDA IPC)
   int transpose_ce = 1;                                 // param "transpose_ce": 1 = transposes as pitched peer copies on the copy engines, 0 = scatter kernels

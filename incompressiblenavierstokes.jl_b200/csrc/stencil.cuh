@@ -195,6 +195,32 @@ __global__ void k_copy_view(View<T> dst, View<const T> src, Geo g, int nc) {
     dst.p[c * dst.sc + k * dst.sz + j * dst.sy + i] = src.p[c * src.sc + k * src.sz + j * src.sy + i];
 }
 
+// the same copy with four cells per thread: 16-byte accesses on the side whose rows are 16-byte aligned (the internal
+// padded / compact layout; the reference layout's rows start 4 or 8 bytes off), scalar accesses on the other.
+// VDST: the destination is the aligned side (import), else the source is (export).  Needs n[0] % 4 == 0.
+template <typename T, bool VDST>
+__global__ void k_copy_view4(View<T> dst, View<const T> src, Geo g, int nc) {
+  const int i = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+  const int j = blockIdx.y * blockDim.y + threadIdx.y;
+  const int k = blockIdx.z;
+  if (i >= g.n[0] || j >= g.n[1]) return;
+  struct alignas(4 * sizeof(T)) V4 { T v[4]; };
+  for (int c = 0; c < nc; c++) {
+    T *d = dst.p + c * dst.sc + k * dst.sz + j * dst.sy + i;
+    const T *s = src.p + c * src.sc + k * src.sz + j * src.sy + i;
+    V4 v;
+    if (VDST) {
+#pragma unroll
+      for (int q = 0; q < 4; q++) v.v[q] = __ldg(s + q);
+      *reinterpret_cast<V4 *>(d) = v;
+    } else {
+      v = *reinterpret_cast<const V4 *>(s);
+#pragma unroll
+      for (int q = 0; q < 4; q++) d[q] = v.v[q];
+    }
+  }
+}
+
 // periodic ghost fill of a reference-layout array: the two ghost layers normal to `axis`, over
 // the FULL extent of the other axes; the source index is wrapped in every axis, which equals the
 // reference's axis-by-axis slab copies (src/boundary_conditions.jl:276-288, 306-318).
