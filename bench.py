@@ -273,6 +273,7 @@ def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False, fused2d=Fal
         "divergence": D + 1.0,
         "pressure_gradient": 2.0 * D + 1,
         "poisson_scale": 2.0,          # half spectrum of complex words, read + written
+        "poisson_sums": 1.0,           # decomposed grid (zline.cuh): the chunk sums read the half spectrum once more
         "cufft_forward": 2.0 * D,      # one read + one write per transformed axis
         "cufft_inverse": 2.0 * D,
         "import_ghosted": 2.0 * D,
@@ -590,16 +591,29 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
         out["closure_fused"] = closure_fused
         if world > 1:
             tb, hb = nvlink_model(D, n, world, esz)
-            tt = sum(kern[k]["ms_per_step"] for k in ("fft_transpose", "fft_pack_unpack", "fft_alltoall") if k in kern)
             ht = kern.get("halo_exchange", {}).get("ms_per_step", 0.0)
-            out["nvlink"] = {"transpose_bytes_per_gpu_step": tb, "halo_bytes_per_gpu_step": hb,
-                             "transpose_ms_per_step": tt, "halo_ms_per_step": ht,
-                             "achieved": tb / (tt * 1e-3) / 1e9 if tt > 0 else None, "unit": "GB/s per GPU, one direction",
-                             "peak": 900.0, "peak_source": "NVLink 5 nominal per direction; a plain peer copy measured 690 GB/s "
-                                                           "(profiles/r1_p2p_probe_2xB200.txt)",
-                             "frac": (tb / (tt * 1e-3) / 1e9 / 900.0) if tt > 0 else None,
-                             "note": "transposes run on a second stream under the in-slab cuFFT; their device time is the sum of "
-                                     "the scatter kernels' event pairs"}
+            flat = [kv.replace(" ", "") for kv in args.param]
+            if "zline=0" not in flat and "p2p=0" not in flat:
+                # default on a decomposed grid: the last axis is solved by two recursions through the slab (zline.cuh); a GPU
+                # reads two complex words per in-plane mode and solve from its neighbours instead of transposing its spectrum
+                modes = float(n[0] // 2 + 1) * (float(n[1]) if D == 3 else 1.0)
+                out["nvlink"] = {"pressure_solve": "transpose-free last-axis solve (zline.cuh)",
+                                 "exchange_bytes_per_gpu_step": 4 * 2 * modes * 2 * esz, "halo_bytes_per_gpu_step": hb,
+                                 "distributed_fft_bytes_per_gpu_step_avoided": tb, "halo_ms_per_step": ht,
+                                 "barrier_ms_per_step": kern.get("fft_alltoall", {}).get("ms_per_step"),
+                                 "achieved": None, "unit": "GB/s per GPU, one direction", "peak": 900.0, "frac": None,
+                                 "note": "the neighbours' sums are read by peer loads inside the solve kernels (timer poisson_scale); "
+                                         "no separate transfer exists to time"}
+            else:
+                tt = sum(kern[k]["ms_per_step"] for k in ("fft_transpose", "fft_pack_unpack", "fft_alltoall") if k in kern)
+                out["nvlink"] = {"pressure_solve": "distributed FFT with transposes", "transpose_bytes_per_gpu_step": tb, "halo_bytes_per_gpu_step": hb,
+                                 "transpose_ms_per_step": tt, "halo_ms_per_step": ht,
+                                 "achieved": tb / (tt * 1e-3) / 1e9 if tt > 0 else None, "unit": "GB/s per GPU, one direction",
+                                 "peak": 900.0, "peak_source": "NVLink 5 nominal per direction; a plain peer copy measured 690 GB/s "
+                                                               "(profiles/r1_p2p_probe_2xB200.txt)",
+                                 "frac": (tb / (tt * 1e-3) / 1e9 / 900.0) if tt > 0 else None,
+                                 "note": "transposes run on other streams under the in-slab cuFFT; their time is the transpose timers' sum "
+                                         "(stream time including waits: a lower bound of the rate)"}
 
     # ---- per-step API: K calls of insb200_rk_step, the loop solve_unsteady runs in Julia (solver.jl:65,75) ----
     if "per_step" in legs:

@@ -17,7 +17,7 @@ SOURCES = [os.path.join(CSRC, "insb200.cu"), os.path.join(CSRC, "temperature.cu"
 # reference's operation order bit for bit (-fmad=false)
 CONTRACTED = {"fast.cu"}
 OBJDIR = os.path.join(HERE, "build")  # git-ignored object cache: only stale translation units are recompiled
-HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "stage2d.cuh", "zsolve.cuh", "zsolve_launch.cuh", "comm.cuh", "fast.cuh", "fast_stage.cuh")] + [
+HEADERS = [os.path.join(CSRC, f) for f in ("ctx.cuh", "stencil.cuh", "tiled.cuh", "tma_stage.cuh", "tma_stage_x2.cuh", "f32x2.cuh", "stage2d.cuh", "zsolve.cuh", "zsolve_launch.cuh", "comm.cuh", "fast.cuh", "fast_stage.cuh", "zline.cuh")] + [
     os.path.join(os.path.dirname(HERE), "include", "insb200.h")
 ]
 

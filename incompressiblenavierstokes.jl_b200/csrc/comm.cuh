@@ -22,7 +22,7 @@ struct PeerPtrs {
 // ranks launch the same sequence of barriers), so a flag is never reset; the compare is wrap-safe.  The spin is
 // bounded (about 4 s): a rank that died must not hang the others' GPUs -- they give up, set flags[63] and the host
 // reports it at the next synchronisation.
-__global__ void __launch_bounds__(32) k_peer_barrier(PeerPtrs F, int rank, int nranks, unsigned epoch, int slot0) {
+static __global__ void __launch_bounds__(32) k_peer_barrier(PeerPtrs F, int rank, int nranks, unsigned epoch, int slot0) {
   const int q = threadIdx.x;
   if (q >= nranks) return;
   __threadfence_system();

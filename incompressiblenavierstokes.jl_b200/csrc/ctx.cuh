@@ -53,13 +53,13 @@ struct Geo {
 enum TimerId {
   TM_IMPORT = 0, TM_EXPORT, TM_BC, TM_MOMENTUM, TM_STAGE, TM_SMAGTENSOR, TM_DIVTENSOR, TM_DIVERGENCE,
   TM_FFT_FWD, TM_FFT_INV, TM_POISSON_SCALE, TM_GRADIENT, TM_REDUCE, TM_HALO, TM_PACK, TM_A2A,
-  TM_MISC, TM_STAGE_GEN, TM_SMAG_FUSED, TM_GHOSTS, TM_SCATTER, TM_COUNT
+  TM_MISC, TM_STAGE_GEN, TM_SMAG_FUSED, TM_GHOSTS, TM_SCATTER, TM_ZSUMS, TM_COUNT
 };
 static const char *const kTimerNames[TM_COUNT] = {
     "import_ghosted", "export_ghosted", "apply_bc", "momentum", "momentum_stage", "smagtensor",
     "divoftensor", "divergence", "cufft_forward", "cufft_inverse", "poisson_scale", "pressure_gradient",
     "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc", "momentum_stage_last", "smagorinsky_fused",
-    "fill_ghosts", "fft_transpose"};
+    "fill_ghosts", "fft_transpose", "poisson_sums"};
 
 struct TimerRec {
   cudaEvent_t a, b;
@@ -157,6 +157,11 @@ struct insb200_ctx {
   std::vector<cudaEvent_t> ce_events;                   // [chunk][destination slot]
   int scatter_blocks = 128;                             // param "scatter_blocks": blocks of the persistent transpose kernels (comm.cuh)
   int fast_barrier = 1;                                 // param "fast_barrier": 0 = ncclAllReduce barriers
+  int zline_req = -1;                                   // param "zline": last-axis solve of a decomposed grid without transposes (zline.cuh); -1 = automatic (on when the peers are mapped), 0 off, 1 on (3-D: also on one rank)
+  int zline_chunks = 0;                                 // param "zline_chunks": sub-chunks per slab (0 = automatic)
+  insb200::i64 cplx_slots = 0;                          // complex words of pcplx / pcplx2 on a decomposed grid
+  void *zl_x = nullptr;                                 // exchange areas of the line solve on ONE rank (no peer buffer there)
+  unsigned zl_count = 0;                                // line solves so far: the two exchange areas alternate
   void *ztw = nullptr;                                  // twiddles exp(-2 pi i t / n_last) of k_zsolve (complex T)
   void *fwork = nullptr;                                // compact vector scratch (insb200_pressure, API ops)
   void *hostio = nullptr;                               // reference-layout device image for *_host calls

@@ -82,6 +82,46 @@ int launch_zsolve_fast(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T i
 template int launch_zsolve_fast<float>(insb200_ctx *, void *, i64, int, int, float, const ZRadix &);
 template int launch_zsolve_fast<double>(insb200_ctx *, void *, i64, int, int, double, const ZRadix &);
 
+// ---- zline.cuh: grid.x over the in-plane modes, grid.y over the sub-chunks of the slab ----------------------------------
+static dim3 zline_grid(const ZlGeo &g) { return dim3((unsigned)((g.pstride + 255) / 256), (unsigned)g.C, 1); }
+template <typename T>
+static void zline_tables(const insb200_ctx *c, const T *&ax, const T *&ay) {
+  ax = (const T *)c->ahat[0];
+  ay = c->D == 3 ? (const T *)c->ahat[1] : nullptr;
+}
+template <typename T>
+int launch_zline_sums(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, const void *S) {
+  const T *ax, *ay;
+  zline_tables<T>(c, ax, ay);
+  k_zline_sums<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (const Cx<T> *)S, ax, ay);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+template <typename T>
+int launch_zline_solve(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S) {
+  const T *ax, *ay;
+  zline_tables<T>(c, ax, ay);
+  const size_t smem = (size_t)g.n * sizeof(double2);
+  if (smem > 48 * 1024) {
+    static bool set[2] = {false, false};
+    if (!set[sizeof(T) == 8]) {
+      INS_CUDA(c, cudaFuncSetAttribute(k_zline_zero<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      set[sizeof(T) == 8] = true;
+    }
+  }
+  k_zline_zero<T><<<1, 256, smem, c->stream>>>(g, X, (Cx<T> *)S);
+  CHECK_LAUNCH(c);
+  k_zline_causal<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
+  CHECK_LAUNCH(c);
+  k_zline_anti<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
+  CHECK_LAUNCH(c);
+  return 0;
+}
+template int launch_zline_sums<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, const void *);
+template int launch_zline_sums<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, const void *);
+template int launch_zline_solve<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+template int launch_zline_solve<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+
 template int launch_stage_fast<float>(insb200_ctx *, const TmaStageArgs<float> &, Geo, double, const void *, const void *);
 template int launch_stage_fast<double>(insb200_ctx *, const TmaStageArgs<double> &, Geo, double, const void *, const void *);
 

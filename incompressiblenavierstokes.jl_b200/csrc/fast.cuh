@@ -3,6 +3,7 @@
 #pragma once
 #include "tiled.cuh"
 #include "tma_stage.cuh"
+#include "zline.cuh"
 
 namespace insb200 {
 
@@ -22,5 +23,13 @@ bool stage_fast_supported(const insb200_ctx *c, bool smag);
 struct ZRadix;
 template <typename T>
 int launch_zsolve_fast(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad);
+
+// fast.cu: the transpose-free last-axis solve of a slab-decomposed spectrum (zline.cuh).  launch_zline_sums = pass 0 (the
+// chunk sums go to this rank's exchange area X.p[g.rank]); the caller then runs the peer barrier; launch_zline_solve =
+// the constant mode's column, the causal and the anticausal pass (they read the other ranks' exchange areas).
+template <typename T>
+int launch_zline_sums(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, const void *S);
+template <typename T>
+int launch_zline_solve(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S);
 
 }  // namespace insb200

@@ -335,7 +335,7 @@ extern "C" int insb200_destroy(insb200_ctx *c) {
   for (auto &p : c->ubuf) if (p) cudaFree(p);
   for (auto &p : c->kbuf) if (p) cudaFree(p);
   for (auto &p : c->ahat) if (p) cudaFree(p);
-  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio, c->ztw, c->tws};
+  void *ptrs[] = {c->force, c->force_g, c->sigma, c->sbuf, c->preal, c->preal2, c->pcplx, c->pcplx2, c->fwork, c->red, c->cufft_work, c->hostio, c->ztw, c->tws, c->zl_x};
   for (void *p : ptrs) if (p) cudaFree(p);
   if (c->red_host) cudaFreeHost(c->red_host);
   for (auto &r : c->recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
@@ -536,6 +536,7 @@ static int ensure_fft(insb200_ctx *c) {
     const i64 slots = std::max((i64)c->nranks * kxmax, (i64)c->nxp) * rows;   // >= rows*nxp and >= nranks*rows*kxl
     INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
     INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
+    c->cplx_slots = slots;
     // form of the transposes: row pieces of at least 1 KB travel well as pitched peer copies
     // (2 GPUs at 512^3 per GPU: 17.6 against 18.9 ms/step); shorter ones (512 B at 4 and 8 GPUs) are packed first
     c->transpose_mode = c->transpose_mode_req >= 0 ? c->transpose_mode_req : ((size_t)c->kxc * 2 * es >= 1024 ? 1 : 2);
@@ -846,6 +847,72 @@ static int launch_zsolve_peer(insb200_ctx *c, T invN, bool local_load) {
 
 #endif  // INSB200_EXPERIMENTAL
 
+// ---- the last axis without transposes (zline.cuh): in-slab transforms -> chunk sums -> barrier -> two recursions --
+static bool zline_active(const insb200_ctx *c) {
+  if (c->zline_req == 0) return false;
+  if (c->nglob[c->last] > 8192) return false;  // k_zline_zero keeps the constant mode's column in shared memory
+  if (c->nranks == 1) return c->zline_req == 1 && c->D == 3;  // one rank: k_zsolve is the default (one pass instead of five)
+  return c->p2p != 0;
+}
+
+template <typename T, int D, typename C>
+static int poisson_line(insb200_ctx *c, T *pr, C *S) {
+  ZlGeo g;
+  g.nkx = c->nxh;
+  g.pitch = (D == 3 && c->nranks > 1) ? c->nxp : c->nxh;
+  g.nky = D == 3 ? c->nloc[1] : 1;
+  g.pstride = (i64)g.pitch * g.nky;
+  g.mloc = c->nloc[c->last];
+  g.P = c->nranks;
+  g.rank = c->rank;
+  g.n = c->nglob[c->last];
+  int ch = 1;
+  if (c->zline_chunks > 0) {
+    if (g.mloc % c->zline_chunks) INS_FAIL(c, "zline_chunks must divide the local extent of the last axis");
+    ch = c->zline_chunks;
+  } else {
+    // enough threads (one per in-plane mode and sub-chunk) to fill the machine a few times over
+    while (g.pstride * ch < 600000 && g.mloc % (2 * ch) == 0 && g.mloc / (2 * ch) >= 16) ch *= 2;
+  }
+  g.C = ch;
+  g.mv = g.mloc / ch;
+  // dz^2 / W in the arithmetic of upload_symbol (W and dz^2 formed in T)
+  T om = T(c->h[0]);
+  for (int a = 1; a < D; a++) om = om * T(c->h[a]);
+  const T dl = T(c->h[c->last]);
+  g.kappa = (double)(dl * dl) / (double)om;
+  g.scale = g.kappa / ((double)c->nglob[0] * (D == 3 ? (double)c->nglob[1] : 1.0));
+  const i64 area = zl_area_words(g);
+  PeerPtrs X;
+  for (int q = 0; q < 16; q++) X.p[q] = nullptr;
+  if (c->nranks == 1) {
+    INS_TRY(dev_alloc(c, &c->zl_x, (size_t)(2 * area) * sizeof(C)));
+    X.p[0] = c->zl_x;
+  } else {
+    if (2 * area > c->cplx_slots) INS_FAIL(c, "line solve: the exchange areas do not fit the peer-mapped buffer (fewer zline_chunks)");
+    for (int q = 0; q < c->nranks; q++) {
+      if (!c->peerB[q]) INS_FAIL(c, "line solve: a peer's exchange buffer is not mapped");
+      X.p[q] = c->peerB[q];
+    }
+  }
+  g.xoff = (i64)(c->zl_count++ & 1u) * area;  // two areas alternate: a peer may still read the previous solve's sums
+  INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
+  {
+    ScopedTimer tm(c, TM_ZSUMS);
+    INS_TRY((launch_zline_sums<T>(c, g, X, S)));
+  }
+  if (c->nranks > 1) {
+    ScopedTimer tm(c, TM_A2A);
+    INS_TRY(peer_barrier(c));
+  }
+  {
+    ScopedTimer tm(c, TM_POISSON_SCALE);
+    INS_TRY((launch_zline_solve<T>(c, g, X, S)));
+  }
+  INS_TRY((exec_inv_in<T, C>(c, S, pr)));
+  return 0;
+}
+
 // ---- spectral Poisson solve on the compact real buffer (in: preal interior = rhs; out: solution) --
 template <typename T, int D>
 static int poisson_solve(insb200_ctx *c) {
@@ -855,6 +922,7 @@ static int poisson_solve(insb200_ctx *c) {
   C *S = (C *)c->pcplx;
   const double ntot = (double)c->nglob[0] * c->nglob[1] * (D == 3 ? c->nglob[2] : 1);
   const T invN = T(1) / T(ntot);
+  if (zline_active(c)) return poisson_line<T, D, C>(c, pr, S);
   if (c->nranks == 1 && D == 3 && zsolve_supported(c)) {
     INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
     INS_TRY((launch_zsolve<T>(c, S, (i64)c->nloc[1] * c->nxh, c->nxh, 0, invN)));
@@ -2343,6 +2411,8 @@ extern "C" int insb200_set_param(insb200_ctx *c, const char *name, double value)
     if (c->plans && c->nranks > 1) INS_FAIL(c, "p2p must be set before the first pressure solve");
     c->p2p_enable = v != 0;
   }
+  else if (k == "zline") { if (v < -1 || v > 1) INS_FAIL(c, "zline must be -1 (automatic), 0 or 1"); c->zline_req = v; }
+  else if (k == "zline_chunks") { if (v < 0) INS_FAIL(c, "zline_chunks must be >= 0"); c->zline_chunks = v; }
   else if (k == "zcols") { if (v != 0 && v != 4 && v != 8 && v != 16) INS_FAIL(c, "zcols must be 0, 4, 8 or 16"); c->zcols = v; }
   else if (k == "zradix16") c->zradix16 = v != 0;
   else if (k == "zthreads") { if (v < 64 || v > 512 || v % 32) INS_FAIL(c, "zthreads must be a multiple of 32 in [64, 512]"); c->zthreads = v; }

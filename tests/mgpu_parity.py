@@ -55,10 +55,10 @@ def big_case(backend):
     sc = ins.Setup(xb, Re=T(2000), backend=backend)
     so.closure_model = o.smagorinsky_closure(so)
     sc.closure_model = ins.smagorinsky_closure(sc)
-    for k in ("MGPU_P2P", "MGPU_FASTBAR", "MGPU_EXACT", "MGPU_TMODE"):
+    for k in ("MGPU_P2P", "MGPU_FASTBAR", "MGPU_EXACT", "MGPU_TMODE", "MGPU_ZLINE", "MGPU_ZLCHUNKS"):
         if k in os.environ:
             sc.ctx.call("insb200_set_param", {"MGPU_P2P": b"p2p", "MGPU_FASTBAR": b"fast_barrier", "MGPU_EXACT": b"exact",
-                                              "MGPU_TMODE": b"transpose_mode"}[k], float(os.environ[k]))
+                                              "MGPU_TMODE": b"transpose_mode", "MGPU_ZLINE": b"zline", "MGPU_ZLCHUNKS": b"zline_chunks"}[k], float(os.environ[k]))
     u0 = o.random_field(so, kp=4, rng=np.random.default_rng(3))
     ul = ins.to_device(ins.local_slab(tile_box(u0, reps, 3), 3, rank, world), sc)
     m = ins.RKMethods.RK44(T=T)
@@ -109,6 +109,10 @@ def main():
             sc.ctx.call("insb200_set_param", b"fast_barrier", float(os.environ["MGPU_FASTBAR"]))
         if "MGPU_EXACT" in os.environ:  # 1 = the bit-exact kernels instead of k_stage3d_fast
             sc.ctx.call("insb200_set_param", b"exact", float(os.environ["MGPU_EXACT"]))
+        if "MGPU_ZLINE" in os.environ:  # last axis of the pressure solve: 1 / -1 = without transposes (zline.cuh, default), 0 = distributed FFT
+            sc.ctx.call("insb200_set_param", b"zline", float(os.environ["MGPU_ZLINE"]))
+        if "MGPU_ZLCHUNKS" in os.environ:
+            sc.ctx.call("insb200_set_param", b"zline_chunks", float(os.environ["MGPU_ZLCHUNKS"]))
         if "MGPU_TMODE" in os.environ:  # transposes: 2 = pack + contiguous peer copies (default), 1 = pitched peer copies, 0 = scatter kernels
             sc.ctx.call("insb200_set_param", b"transpose_mode", float(os.environ["MGPU_TMODE"]))
         sc.ctx.call("insb200_set_param", b"fft_pipe_min_ranks", 2.0)  # exercise the pipelined transposes at any world size
