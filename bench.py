@@ -273,7 +273,7 @@ def kernel_words(D, smag, force, nstages=4, tma=False, zsolve=False, fused2d=Fal
         "divergence": D + 1.0,
         "pressure_gradient": 2.0 * D + 1,
         "poisson_scale": 2.0,          # half spectrum of complex words, read + written
-        "poisson_sums": 1.0,           # decomposed grid (zline.cuh): the chunk sums read the half spectrum once more
+        "poisson_forward": 2.0,        # decomposed grid (zline.cuh): the causal pass, read + write of the half spectrum; "poisson_scale" is the anticausal one
         "cufft_forward": 2.0 * D,      # one read + one write per transformed axis
         "cufft_inverse": 2.0 * D,
         "import_ghosted": 2.0 * D,
@@ -451,6 +451,17 @@ def parity_check(ins, backend, wl, dist, params=()):
     return rec, bool(ok)
 
 
+def stable_dt(wl, n, base_n, dt_cfl):
+    """Fixed step of a throughput run: the configured one, capped by half the reference's CFL bound (get_cfl_timestep!,
+    solver.jl:101-125) and by the RK44 stability limit of the diffusion operator.  The reference's bound is per axis
+    (Re dx^2 / 2); in 3-D the stiffest mode sees the SUM of the axes' eigenvalues, -nu * sum_d 4 / dx_d^2, and RK44 is stable
+    on the negative real axis only up to 2.785: at 1024^3, Re = 1000 half the CFL bound gives z = -3.0, amplification 1.375
+    per step -- the (pi, pi, pi) mode grows from round-off to overflow within about a hundred steps (seen once in the
+    8-GPU run of round 2; throughput does not depend on dt, the solution must stay finite)."""
+    nu_sum = sum(4.0 * float(m) ** 2 for m in n) / wl["Re"]   # unit domain: dx_d = 1 / n_d
+    return min(wl["dt"] * wl["n"] / base_n, dt_cfl, 0.8 * 2.785 / nu_sum)
+
+
 def nvlink_model(D, n, world, esz):
     """Algorithmic NVLink bytes sent per GPU per RK44 step: distributed-FFT transposes and halo planes."""
     if world == 1:
@@ -486,7 +497,7 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
     # (get_cfl_timestep!, solver.jl:101-125) of the start field -- random_field(A = 1, kp = 10) reaches |u| = 16, for which
     # the examples step adaptively; throughput does not depend on dt
     dt_cfl = 0.5 * float(ins.get_cfl_timestep_(None, u, setup))
-    dt = min(wl["dt"] * wl["n"] / base_n, dt_cfl)
+    dt = stable_dt(wl, n, base_n, dt_cfl)
     lib, h = setup.ctx.lib, setup.ctx.h
     K, W = args.steps, args.warmup
     cells = float(np.prod([float(m) for m in n]))

@@ -59,7 +59,7 @@ static const char *const kTimerNames[TM_COUNT] = {
     "import_ghosted", "export_ghosted", "apply_bc", "momentum", "momentum_stage", "smagtensor",
     "divoftensor", "divergence", "cufft_forward", "cufft_inverse", "poisson_scale", "pressure_gradient",
     "reduce", "halo_exchange", "fft_pack_unpack", "fft_alltoall", "misc", "momentum_stage_last", "smagorinsky_fused",
-    "fill_ghosts", "fft_transpose", "poisson_sums"};
+    "fill_ghosts", "fft_transpose", "poisson_forward"};
 
 struct TimerRec {
   cudaEvent_t a, b;

@@ -90,15 +90,15 @@ static void zline_tables(const insb200_ctx *c, const T *&ax, const T *&ay) {
   ay = c->D == 3 ? (const T *)c->ahat[1] : nullptr;
 }
 template <typename T>
-int launch_zline_sums(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, const void *S) {
+int launch_zline_forward(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S) {
   const T *ax, *ay;
   zline_tables<T>(c, ax, ay);
-  k_zline_sums<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (const Cx<T> *)S, ax, ay);
+  k_zline_forward<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
   CHECK_LAUNCH(c);
   return 0;
 }
 template <typename T>
-int launch_zline_solve(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S) {
+int launch_zline_backward(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S) {
   const T *ax, *ay;
   zline_tables<T>(c, ax, ay);
   const size_t smem = (size_t)g.n * sizeof(double2);
@@ -109,18 +109,16 @@ int launch_zline_solve(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *
       set[sizeof(T) == 8] = true;
     }
   }
-  k_zline_zero<T><<<1, 256, smem, c->stream>>>(g, X, (Cx<T> *)S);
+  k_zline_zero<T><<<(g.mloc + kZlZeroWarps - 1) / kZlZeroWarps, 32 * kZlZeroWarps, smem, c->stream>>>(g, X, (Cx<T> *)S);
   CHECK_LAUNCH(c);
-  k_zline_causal<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
-  CHECK_LAUNCH(c);
-  k_zline_anti<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
+  k_zline_backward<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);
   CHECK_LAUNCH(c);
   return 0;
 }
-template int launch_zline_sums<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, const void *);
-template int launch_zline_sums<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, const void *);
-template int launch_zline_solve<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
-template int launch_zline_solve<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+template int launch_zline_forward<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+template int launch_zline_forward<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+template int launch_zline_backward<float>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
+template int launch_zline_backward<double>(insb200_ctx *, const ZlGeo &, const PeerPtrs &, void *);
 
 template int launch_stage_fast<float>(insb200_ctx *, const TmaStageArgs<float> &, Geo, double, const void *, const void *);
 template int launch_stage_fast<double>(insb200_ctx *, const TmaStageArgs<double> &, Geo, double, const void *, const void *);

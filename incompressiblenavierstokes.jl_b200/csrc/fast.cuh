@@ -24,12 +24,12 @@ struct ZRadix;
 template <typename T>
 int launch_zsolve_fast(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0, T invN, const ZRadix &rad);
 
-// fast.cu: the transpose-free last-axis solve of a slab-decomposed spectrum (zline.cuh).  launch_zline_sums = pass 0 (the
-// chunk sums go to this rank's exchange area X.p[g.rank]); the caller then runs the peer barrier; launch_zline_solve =
-// the constant mode's column, the causal and the anticausal pass (they read the other ranks' exchange areas).
+// fast.cu: the transpose-free last-axis solve of a slab-decomposed spectrum (zline.cuh).  launch_zline_forward = pass A (the
+// chunk sums go to this rank's exchange area X.p[g.rank]); the caller then runs the peer barrier; launch_zline_backward =
+// the constant mode's column and pass B (they read the other ranks' exchange areas).
 template <typename T>
-int launch_zline_sums(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, const void *S);
+int launch_zline_forward(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S);
 template <typename T>
-int launch_zline_solve(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S);
+int launch_zline_backward(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, void *S);
 
 }  // namespace insb200

@@ -535,8 +535,10 @@ static int ensure_fft(insb200_ctx *c) {
     const i64 kxmax = c->nxh - (i64)(c->nranks - 1) * c->kxc;                 // the last rank's (largest) column count
     const i64 slots = std::max((i64)c->nranks * kxmax, (i64)c->nxp) * rows;   // >= rows*nxp and >= nranks*rows*kxl
     INS_TRY(dev_alloc(c, &c->pcplx, (size_t)slots * 2 * es));
-    INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots * 2 * es));
-    c->cplx_slots = slots;
+    // (pcplx2 is also the exchange buffer of the line solve, zline.cuh: room for two areas of up to 4 sub-chunks on tiny grids)
+    const i64 slots2 = std::max(slots, 16 * (D == 3 ? (i64)c->nxp * c->nloc[1] : (i64)c->nxh) + 64);
+    INS_TRY(dev_alloc(c, &c->pcplx2, (size_t)slots2 * 2 * es));
+    c->cplx_slots = slots2;
     // form of the transposes: row pieces of at least 1 KB travel well as pitched peer copies
     // (2 GPUs at 512^3 per GPU: 17.6 against 18.9 ms/step); shorter ones (512 B at 4 and 8 GPUs) are packed first
     c->transpose_mode = c->transpose_mode_req >= 0 ? c->transpose_mode_req : ((size_t)c->kxc * 2 * es >= 1024 ? 1 : 2);
@@ -899,7 +901,7 @@ static int poisson_line(insb200_ctx *c, T *pr, C *S) {
   INS_TRY((exec_fwd_in<T, C>(c, pr, S)));
   {
     ScopedTimer tm(c, TM_ZSUMS);
-    INS_TRY((launch_zline_sums<T>(c, g, X, S)));
+    INS_TRY((launch_zline_forward<T>(c, g, X, S)));
   }
   if (c->nranks > 1) {
     ScopedTimer tm(c, TM_A2A);
@@ -907,7 +909,7 @@ static int poisson_line(insb200_ctx *c, T *pr, C *S) {
   }
   {
     ScopedTimer tm(c, TM_POISSON_SCALE);
-    INS_TRY((launch_zline_solve<T>(c, g, X, S)));
+    INS_TRY((launch_zline_backward<T>(c, g, X, S)));
   }
   INS_TRY((exec_inv_in<T, C>(c, S, pr)));
   return 0;

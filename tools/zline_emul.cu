@@ -61,7 +61,7 @@ static double run(int nx, int ny, int n, int P, int C, bool verbose) {
   PeerPtrs px;
   for (int r = 0; r < 16; r++) px.p[r] = r < P ? (void *)X[r].data() : nullptr;
   const T *ayp = D == 3 ? ay.data() : nullptr;
-  for (int r = 0; r < P; r++) { g.rank = r; for (int c = 0; c < C; c++) for (long long i = 0; i < g.pstride; i++) zl_pass0<T>(g, px, S[r].data(), ax.data(), ayp, i, c); }
+  for (int r = 0; r < P; r++) { g.rank = r; for (int c = 0; c < C; c++) for (long long i = 0; i < g.pstride; i++) zl_passA<T>(g, px, S[r].data(), ax.data(), ayp, i, c); }
   // (barrier)
   for (int r = 0; r < P; r++) {  // the constant in-plane mode, as k_zline_zero does it
     g.rank = r;
@@ -75,13 +75,16 @@ static double run(int nx, int ny, int n, int P, int C, bool verbose) {
     }
     mx /= n; my /= n;
     for (int jl = 0; jl < g.mloc; jl++) {
-      double pxv, pyv;
-      zl_zero_point<double2>(col.data(), n, r * g.mloc + jl, mx, my, g.scale, pxv, pyv);
-      S[r][(size_t)jl * g.pstride] = Cx<T>{(T)pxv, (T)pyv};
+      double sx = 0, sy = 0;
+      for (int lane = 0; lane < 32; lane++) {  // the lanes of the warp that owns this point
+        double ax_, ay_;
+        zl_zero_point<double2>(col.data(), n, r * g.mloc + jl, lane, 32, mx, my, ax_, ay_);
+        sx += ax_; sy += ay_;
+      }
+      S[r][(size_t)jl * g.pstride] = Cx<T>{(T)(g.scale * sx), (T)(g.scale * sy)};
     }
   }
-  for (int r = 0; r < P; r++) { g.rank = r; for (int c = 0; c < C; c++) for (long long i = 0; i < g.pstride; i++) zl_pass1<T>(g, px, S[r].data(), ax.data(), ayp, i, c); }
-  for (int r = 0; r < P; r++) { g.rank = r; for (int c = 0; c < C; c++) for (long long i = 0; i < g.pstride; i++) zl_pass2<T>(g, px, S[r].data(), ax.data(), ayp, i, c); }
+  for (int r = 0; r < P; r++) { g.rank = r; for (int c = 0; c < C; c++) for (long long i = 0; i < g.pstride; i++) zl_passB<T>(g, px, S[r].data(), ax.data(), ayp, i, c); }
   // reference: per mode, DFT along the line in double
   double err2 = 0, ref2 = 0, emax = 0, rmax = 0;
   std::vector<std::complex<double>> f(n), F(n), p(n);
