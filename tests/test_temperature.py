@@ -266,7 +266,7 @@ def test_rk_steps_with_temperature(n, smag, diss, method, T):
     tol = TOL[T]
     compare("u after 5 steps", ins.to_host(stc.u), st.u, tol)
     compare("temp after 5 steps", ins.to_host(stc.temp), st.temp, tol)
-    compare("p of the last stage", ins.to_host(pc)[g.Ip], p[g.Ip], 20 * tol, target=tol)
+    compare("p of the last stage", ins.to_host(pc)[g.Ip], p[g.Ip], tol)  # measured <= 7e-15 / 3.3e-6 (profiles/r2_tolerances.txt)
     assert abs(float(stc.t) - float(st.t)) <= 4 * np.finfo(T).eps and stc.n == nstep
     div = o.divergence(ins.to_host(stc.u), so)[g.Ip]
     assert np.abs(div).max() < 2e3 * np.finfo(T).eps * max(1.0, np.abs(st.u).max()) * max(n)
