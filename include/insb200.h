@@ -254,8 +254,15 @@ int insb200_set_variant(insb200_ctx *ctx, int variant);
  *   Poisson solve:  "zsolve" 0|1 (fused last-axis kernel instead of cuFFT's z pass; differs from cuFFT by round-off),
  *                   "zcols" 0|4|8|16, "zthreads", "zradix16" 0|1 (Float32 radix-16 passes; round-off),
  *                   "fft_chunk" planes per cufftExec (0 = whole slab), "fft_pipe" / "fft_pipe_min_ranks"
- *   multi-GPU:      "p2p" 0|1 (peer-store transposes over CUDA IPC; before the first solve), "p2p_halo" 0|1,
- *                   "p2p_fused" 0|1|2
+ *   arithmetic:     "exact" 0|1 (1: the kernels built without FMA contraction, bit-identical to the oracle; 0, default: the
+ *                   contracted kernels of fast.cu, north_star's tolerance), "fast_gen" 0|1
+ *   multi-GPU:      "p2p" 0|1 (exchange over peer memory mapped with CUDA IPC; 0: NCCL send/recv; before the first solve),
+ *                   "p2p_halo" 0|1, "fast_barrier" 0|1 (flag words in peer memory | 4-byte ncclAllReduce),
+ *                   "zline" -1|0|1 (last axis of the pressure solve without transposes, csrc/zline.cuh: automatic = on when
+ *                   the peers are mapped | distributed FFT | on, 3-D also on one rank; differs from the FFT by round-off),
+ *                   "zline_chunks" sub-chunks per slab (0 = automatic),
+ *                   distributed FFT: "transpose_mode" -1|0|1|2 (automatic | scatter kernels | pitched peer copies | pack +
+ *                   contiguous peer copies), "scatter_blocks"; "stage_x2" / "p2p_fused" need -DINSB200_EXPERIMENTAL
  *   "graphs" 1|0|-1 (CUDA-graph replay of whole steps: on, off, automatic for slabs of <= 2^22 cells). */
 int insb200_set_param(insb200_ctx *ctx, const char *name, double value);
 

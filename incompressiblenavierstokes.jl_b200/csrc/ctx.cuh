@@ -157,6 +157,7 @@ struct insb200_ctx {
   std::vector<cudaEvent_t> ce_events;                   // [chunk][destination slot]
   int scatter_blocks = 128;                             // param "scatter_blocks": blocks of the persistent transpose kernels (comm.cuh)
   int fast_barrier = 1;                                 // param "fast_barrier": 0 = ncclAllReduce barriers
+  std::map<const void *, size_t> smem_attr;             // dynamic shared memory opted into, per kernel: a context belongs to ONE device, a process-wide flag would not do
   int zline_req = -1;                                   // param "zline": last-axis solve of a decomposed grid without transposes (zline.cuh); -1 = automatic (on when the peers are mapped), 0 off, 1 on (3-D: also on one rank)
   int zline_chunks = 0;                                 // param "zline_chunks": sub-chunks per slab (0 = automatic)
   insb200::i64 cplx_slots = 0;                          // complex words of pcplx / pcplx2 on a decomposed grid
@@ -241,6 +242,16 @@ inline int fail(insb200_ctx *c, const char *file, int line, const std::string &m
     if (r_ != ncclSuccess)                                                                      \
       return ::insb200::fail((ctx), __FILE__, __LINE__, std::string("NCCL: ") + ncclGetErrorString(r_) + " in " #call); \
   } while (0)
+// opt a kernel into `bytes` of dynamic shared memory once per context (and again if a launch needs more)
+#define INS_DYN_SMEM(c, kern, bytes)                                                                                  \
+  do {                                                                                                                \
+    size_t &cur_ = (c)->smem_attr[reinterpret_cast<const void *>(kern)];                                              \
+    if ((size_t)(bytes) > cur_) {                                                                                     \
+      INS_CUDA((c), cudaFuncSetAttribute((kern), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));         \
+      cur_ = (size_t)(bytes);                                                                                         \
+    }                                                                                                                 \
+  } while (0)
+
 #ifndef CHECK_LAUNCH
 #define CHECK_LAUNCH(c)                      \
   do {                                       \

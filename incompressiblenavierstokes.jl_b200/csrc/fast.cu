@@ -46,11 +46,7 @@ static int launch_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, double thet
   const int bps = (SM || GEN || sizeof(T) == 8) ? 1 : 2;
   const int zc = auto_zchunk(c, c->zchunk, tiles, bps, -Cfg::R0);
   auto kern = k_stage3d_fast<T, PG, SM, GEN>;
-  static int attr_dev = -1;  // per device: a second context on another device needs its own opt-in
-  if (attr_dev != c->device) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-    attr_dev = c->device;
-  }
+  INS_DYN_SMEM(c, kern, Cfg::SMEM);
   dim3 grd(c->nloc[0] / Cfg::TX, c->nloc[1] / Cfg::TY, (c->nloc[2] + zc - 1) / zc), blk(Cfg::TX, Cfg::NTY, 1);
   kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, a, make_fastk<T>(c, theta), g, zc, c->org[0], c->org[1], c->org[2]);
   CHECK_LAUNCH(c);
@@ -102,13 +98,7 @@ int launch_zline_backward(insb200_ctx *c, const ZlGeo &g, const PeerPtrs &X, voi
   const T *ax, *ay;
   zline_tables<T>(c, ax, ay);
   const size_t smem = (size_t)g.n * sizeof(double2);
-  if (smem > 48 * 1024) {
-    static bool set[2] = {false, false};
-    if (!set[sizeof(T) == 8]) {
-      INS_CUDA(c, cudaFuncSetAttribute(k_zline_zero<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      set[sizeof(T) == 8] = true;
-    }
-  }
+  if (smem > 48 * 1024) INS_DYN_SMEM(c, k_zline_zero<T>, smem);
   k_zline_zero<T><<<(g.mloc + kZlZeroWarps - 1) / kZlZeroWarps, 32 * kZlZeroWarps, smem, c->stream>>>(g, X, (Cx<T> *)S);
   CHECK_LAUNCH(c);
   k_zline_backward<T><<<zline_grid(g), 256, 0, c->stream>>>(g, X, (Cx<T> *)S, ax, ay);

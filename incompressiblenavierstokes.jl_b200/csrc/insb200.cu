@@ -821,11 +821,7 @@ static int launch_zsolve_peer_i(insb200_ctx *c, T invN, const ZRadix &rad, bool 
   for (int q = 0; q < P; q++) pm.m[q] = it->second[q];
   const size_t smem = 128 + (size_t)(nz * COLS + nz) * sizeof(Cx<T>) + (size_t)nz * sizeof(T) + 16;
   auto kern = k_zsolve_peer<T, COLS>;
-  static size_t attr = 0;
-  if (smem > attr) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = smem;
-  }
+  INS_DYN_SMEM(c, kern, smem);
   const int tiles_x = (c->kxl + CX - 1) / CX, tiles_y = (ny + CY - 1) / CY;
   kern<<<(unsigned)(tiles_x * tiles_y), c->zthreads, smem, c->stream>>>(pm, it->second[P], local_load ? 1 : 0, (const Cx<T> *)c->ztw, (const T *)c->ahat[0],
                                                                       (const T *)c->ahat[1], (const T *)c->ahat[2], nz, nzl, P, lcx,
@@ -1669,11 +1665,7 @@ static int launch_stage3d(insb200_ctx *c, const StageArgs<T> &a, Geo g, T visc, 
   typedef Tile3<TX, TY> TL;
   const size_t smem = (size_t)(12 * TL::NP + 2 * TY * (TX + 1) + 2 * (TY + 1) * TX) * sizeof(T);
   auto kern = k_stage3d<T, SMAG, PGRAD, TX, TY>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  INS_DYN_SMEM(c, kern, smem);
   const int zc = std::max(2, std::min(c->zchunk > 0 ? c->zchunk : 64, c->nloc[2]));
   dim3 grd(c->nloc[0] / TX, c->nloc[1] / TY, (c->nloc[2] + zc - 1) / zc), blk(TX, TY, 1);
   kern<<<grd, blk, smem, c->stream>>>(a, g, visc, rh, volume<T>(c), zc);
@@ -1749,12 +1741,8 @@ static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T
   if constexpr (std::is_same<T, float>::value) if (c->stage_x2) {  // two cells per thread on packed FP32 (tma_stage_x2.cuh)
     auto kex = k_stage3d_tma_x2<f2t<true>, PG, SA, GEN, kTX, kTY, kNS>;    // 1: exact (bit-identical to the scalar kernel)
     auto kfu = k_stage3d_tma_x2<f2t<false>, PG, SA, GEN, kTX, kTY, kNS>;   // 2: products contracted into FFMA2
-    static bool attr2_set = false;
-    if (!attr2_set) {
-      INS_CUDA(c, cudaFuncSetAttribute(kex, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-      INS_CUDA(c, cudaFuncSetAttribute(kfu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-      attr2_set = true;
-    }
+    INS_DYN_SMEM(c, kex, Cfg::SMEM);
+    INS_DYN_SMEM(c, kfu, Cfg::SMEM);
     (c->stage_x2 == 1 ? kex : kfu)<<<grd, dim3(kTX, kTY / 2, 1), Cfg::SMEM, c->stream>>>(tu, tp, a, g, visc, rh, volume<T>(c), zc, c->org[0],
                                                                                        c->org[1], c->org[2]);
     CHECK_LAUNCH(c);
@@ -1762,11 +1750,7 @@ static int launch_stage_tma_i(insb200_ctx *c, const TmaStageArgs<T> &a, Geo g, T
   }
 #endif
   auto kern = k_stage3d_tma<T, PG, SA, GEN, kTX, kTY, kNS>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-    attr_set = true;
-  }
+  INS_DYN_SMEM(c, kern, Cfg::SMEM);
   kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, a, g, visc, rh, volume<T>(c), zc, c->org[0], c->org[1], c->org[2]);
   CHECK_LAUNCH(c);
   return 0;
@@ -1800,11 +1784,7 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
       INS_TRY(get_tmap(c, ubase, 3, Cfg2::Pipe::BX, 8 + 4, &tu8));
       INS_TRY(get_tmap(c, pbase, 1, Cfg2::Pipe::BX, 8 + 5, &tp8));
       auto kern2 = k_smag3d_v2<T, PG, kTX, 8>;
-      static bool attr8_set = false;
-      if (!attr8_set) {
-        INS_CUDA(c, cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM));
-        attr8_set = true;
-      }
+      INS_DYN_SMEM(c, kern2, Cfg2::SMEM);
       dim3 grd2(c->nloc[0] / kTX, c->nloc[1] / 8, (c->nloc[2] + zc2 - 1) / zc2), blk2(kTX, 8 + 4, 1);
       kern2<<<grd2, blk2, Cfg2::SMEM, c->stream>>>(tu8, tp8, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc2, c->org[0],
                                                 c->org[1], c->org[2]);
@@ -1814,11 +1794,7 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
     // one block of 32 x 20 threads per SM
     typedef Smag2Cfg<T, PG, kTX, kTY> Cfg2;
     auto kern2 = k_smag3d_v2<T, PG, kTX, kTY>;
-    static bool attr2_set = false;
-    if (!attr2_set) {
-      INS_CUDA(c, cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM));
-      attr2_set = true;
-    }
+    INS_DYN_SMEM(c, kern2, Cfg2::SMEM);
     dim3 grd2(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc2 - 1) / zc2), blk2(kTX, kTY + 4, 1);
     kern2<<<grd2, blk2, Cfg2::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc2, c->org[0], c->org[1],
                                               c->org[2]);
@@ -1826,11 +1802,7 @@ static int launch_smag_tma_i(insb200_ctx *c, T *sout, Geo g, T c_eddy, Rh<T> rh,
     return 0;
   }
   auto kern = k_smag3d_tma<T, PG, kTX, kTY>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
-    attr_set = true;
-  }
+  INS_DYN_SMEM(c, kern, Cfg::SMEM);
   const int zc = auto_zchunk(c, c->zchunk, (c->nloc[0] / kTX) * (c->nloc[1] / kTY), sizeof(T) == 4 ? 2 : 1, 5);
   dim3 grd(c->nloc[0] / kTX, c->nloc[1] / kTY, (c->nloc[2] + zc - 1) / zc), blk(kTX, kTY, 1);
   kern<<<grd, blk, Cfg::SMEM, c->stream>>>(tu, tp, sout, c->csy, c->csz, c->ccomp, g, c_eddy, rh, zc, c->org[0], c->org[1],

@@ -38,11 +38,7 @@ static int launch_zsolve_i(insb200_ctx *c, void *S, i64 ncols, int nxw, int kx0,
       c->tmaps[key] = tm;
     }
   }
-  static size_t attr = 0;
-  if (smem > attr) {
-    INS_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr = smem;
-  }
+  INS_DYN_SMEM(c, kern, smem);
   const unsigned nb = (unsigned)((ncols + COLS - 1) / COLS);
   kern<<<nb, c->zthreads, smem, c->stream>>>(tm, (const Cx<T> *)c->ztw, (const T *)c->ahat[0], (const T *)c->ahat[1],
                                      (const T *)c->ahat[2], nz, ncols, nxw, kx0, T(-1) / invN, rad);
