@@ -848,7 +848,9 @@ static int launch_zsolve_peer(insb200_ctx *c, T invN, bool local_load) {
 // ---- the last axis without transposes (zline.cuh): in-slab transforms -> chunk sums -> barrier -> two recursions --
 static bool zline_active(const insb200_ctx *c) {
   if (c->zline_req == 0) return false;
-  if (c->nglob[c->last] > 8192) return false;  // k_zline_zero keeps the constant mode's column in shared memory
+  // k_zline_zero keeps the constant mode's column in shared memory (16 B per point): automatic up to the 48 KB every
+  // launch may use (measured: lines of up to 1024 points); up to 128 KB on request ("zline" = 1)
+  if (c->nglob[c->last] > (c->zline_req == 1 ? 8192 : 3072)) return false;
   if (c->nranks == 1) return c->zline_req == 1 && c->D == 3;  // one rank: k_zsolve is the default (one pass instead of five)
   return c->p2p != 0;
 }
