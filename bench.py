@@ -451,6 +451,30 @@ def parity_check(ins, backend, wl, dist, params=()):
     return rec, bool(ok)
 
 
+class BlowUp(Exception):
+    """the timed solution became non-finite (decided collectively: every rank raises it at the same point)"""
+
+
+def measure_with_fallback(run, args, world, rank, remeasured, name):
+    """A non-finite run is invalid and is re-measured ONCE, on a decomposed grid with the other pressure solver (the
+    distributed FFT instead of the transpose-free line solve; `run` reads args.param): the JSON line then says so in
+    "remeasured".  One rank, an explicit solver choice, or a second failure end the run."""
+    try:
+        return run()
+    except BlowUp as e:
+        flat = [kv.replace(" ", "") for kv in args.param]
+        if world == 1 or "zline=0" in flat or "p2p=0" in flat:
+            raise SystemExit(f"bench.py: the solution blew up ({e}) -- invalid run")
+        if rank == 0:
+            print(f"bench.py: {e}; measuring again with --param zline=0", file=sys.stderr, flush=True)
+        remeasured[name] = {"why": str(e), "with": "zline=0 (distributed FFT)"}
+        args.param = list(args.param) + ["zline=0"]
+        try:
+            return run()
+        except BlowUp as e2:
+            raise SystemExit(f"bench.py: the solution blew up again ({e2}) -- invalid run")
+
+
 def stable_dt(wl, n, base_n, dt_cfl):
     """Fixed step of a throughput run: the configured one, capped by half the reference's CFL bound (get_cfl_timestep!,
     solver.jl:101-125) and by the RK44 stability limit of the diffusion operator.  The reference's bound is per axis
@@ -549,8 +573,12 @@ def measure(ins, backend, wl, args, base_n, dist, workload_name, legs=("timers",
     clocks = sampler.stop(w0, w1) if sampler else None
     ms_step = ms / K
     value = cells / (ms_step * 1e-3) / 1e6
-    if not bool(torch.isfinite(u).all()):
-        raise SystemExit("bench.py: the solution blew up (non-finite u) -- invalid run")
+    if max_over_ranks(0.0 if bool(torch.isfinite(u).all()) else 1.0) > 0.5:  # the same verdict on every rank
+        barrier()
+        setup.ctx.close()  # collective teardown, as at the end of a good run
+        del u
+        torch.cuda.empty_cache()
+        raise BlowUp(f"{workload_name}: non-finite u after {W + K} steps and the clock-sampling repeats, dt = {dt:g}")
     out = {"n": n, "cells": cells, "ms_step": ms_step, "value": value, "launches": int(launches), "ffts": int(ffts),
            "graph_replays": int(graph_replays), "clocks": clocks, "dt": dt, "init": init, "theta": theta}
     esz = np.dtype(T).itemsize
@@ -703,14 +731,19 @@ def run_ours(args, wl):
                                   "error": "parity self-check against the oracle FAILED: nothing was timed"}), flush=True)
             raise SystemExit(3)
 
-    m = measure(ins, backend, wl, args, base_n, dist, args.workload)
+    remeasured = {}
+
+    def measured(wl_, name, **kw):
+        return measure_with_fallback(lambda: measure(ins, backend, wl_, args, base_n, dist, name, **kw), args, world, rank, remeasured, name)
+
+    m = measured(wl, args.workload)
 
     # ---- config 5 (north_star's target): TaylorGreenVortex3D 1024^3 Float32 on 8 GPUs ------------
     config5 = None
     if (world == 8 and args.workload == "dt3d_smag" and not args.n) or args.also_tgv:
         wl5 = WORKLOADS["tgv3d"]
         p5, ok5 = (None, True) if args.no_parity else parity_check(ins, backend, wl5, dist, args.param)
-        m5 = measure(ins, backend, wl5, args, base_n, dist, "tgv3d", legs=("timers",))
+        m5 = measured(wl5, "tgv3d", legs=("timers",))
         if rank == 0:
             config5 = {"workload": wl5["title"], "grid": list(m5["n"]), "n_gpus": world, "ms_per_step": m5["ms_step"],
                        "steps_per_s": 1e3 / m5["ms_step"], "value": m5["value"], "unit": "Mcell-updates/s",
@@ -749,7 +782,7 @@ def run_ours(args, wl):
         "gpu_launches": m["launches"], "cufft_execs": m["ffts"],
         "graph_replays": m["graph_replays"], "workspace_bytes_per_gpu": m["workspace_bytes"],
         "roofline": m.get("roofline"), "step_roofline": m["step_roofline"], "closure_fused": m.get("closure_fused"),
-        "nvlink": m.get("nvlink"), "parity_check": parity, "config5": config5,
+        "nvlink": m.get("nvlink"), "parity_check": parity, "config5": config5, "remeasured": remeasured or None,
         "kernels": m.get("kernels"), "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)

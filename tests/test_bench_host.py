@@ -36,3 +36,31 @@ def test_half_the_per_axis_bound_alone_is_unstable_in_3d():
 def test_kernel_word_model_has_the_line_solve_passes():
     w = bench.kernel_words(3, False, False, tma=True, zsolve=True)
     assert w["poisson_forward"] == 2.0 and w["poisson_scale"] == 2.0 and w["cufft_forward"] == 4.0
+
+
+def test_a_non_finite_run_is_measured_again_once_with_the_other_solver():
+    import types
+
+    calls = []
+
+    def run_factory(fail_times):
+        def run():
+            calls.append(list(args.param))
+            if len(calls) <= fail_times:
+                raise bench.BlowUp("tgv3d: non-finite u")
+            return {"ok": True}
+        return run
+
+    args = types.SimpleNamespace(param=["fft_pipe=4"])
+    rem = {}
+    assert bench.measure_with_fallback(run_factory(1), args, 8, 1, rem, "tgv3d") == {"ok": True}
+    assert calls == [["fft_pipe=4"], ["fft_pipe=4", "zline=0"]] and rem["tgv3d"]["with"].startswith("zline=0")
+    calls.clear()
+    with pytest.raises(SystemExit):  # fails with both solvers
+        bench.measure_with_fallback(run_factory(2), types.SimpleNamespace(param=[]), 8, 1, {}, "tgv3d")
+    calls.clear()
+    with pytest.raises(SystemExit):  # one GPU: nothing to fall back to
+        bench.measure_with_fallback(run_factory(1), types.SimpleNamespace(param=[]), 1, 0, {}, "tgv3d")
+    calls.clear()
+    with pytest.raises(SystemExit):  # the caller chose the solver
+        bench.measure_with_fallback(run_factory(1), types.SimpleNamespace(param=["zline = 0"]), 8, 0, {}, "tgv3d")
