@@ -28,9 +28,9 @@ def emul(tmp_path_factory):
 
 # nx ny n P C: one rank, ranks only, ranks x sub-chunks, sizes that are not powers of two, the 2-D case (ny = 1), a line
 # long enough that the lowest modes couple every chunk with every other one, chunks so long (and modes so stiff) that
-# rho^j underflows inside a chunk
+# rho^j underflows inside a chunk, chunks of two planes and of one
 @pytest.mark.parametrize("args", [(16, 8, 32, 1, 1), (16, 8, 32, 4, 1), (16, 8, 64, 4, 2), (12, 6, 48, 2, 3), (20, 1, 60, 3, 2),
-                                  (32, 1, 64, 2, 4), (64, 4, 256, 8, 2), (16, 4, 1024, 2, 1), (256, 1, 64, 2, 1)], ids=str)
+                                  (32, 1, 64, 2, 4), (64, 4, 256, 8, 2), (16, 4, 1024, 2, 1), (256, 1, 64, 2, 1), (16, 8, 16, 4, 2), (8, 4, 8, 8, 1)], ids=str)
 def test_line_solve_code_on_host(emul, args):
     res = subprocess.run([emul] + [str(a) for a in args], capture_output=True, text=True)
     assert res.returncode == 0 and "line solve agrees" in res.stdout, res.stdout + res.stderr
