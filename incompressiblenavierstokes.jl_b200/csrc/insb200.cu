@@ -871,8 +871,10 @@ static int poisson_line(insb200_ctx *c, T *pr, C *S) {
     if (g.mloc % c->zline_chunks) INS_FAIL(c, "zline_chunks must divide the local extent of the last axis");
     ch = c->zline_chunks;
   } else {
-    // enough threads (one per in-plane mode and sub-chunk) to fill the machine a few times over
-    while (g.pstride * ch < 600000 && g.mloc % (2 * ch) == 0 && g.mloc / (2 * ch) >= 16) ch *= 2;
+    // enough threads (one per in-plane mode and sub-chunk) to fill the machine, and no more: every sub-chunk adds sums to
+    // exchange and a term to the chains (8 GPUs, 1024^3, 540 k modes per plane: 16.06 / 16.29 / 16.82 ms/step with 1 / 2 / 4
+    // sub-chunks, profiles/r2_sweep_19_8gpu_zline.txt)
+    while (g.pstride * ch < 300000 && g.mloc % (2 * ch) == 0 && g.mloc / (2 * ch) >= 16) ch *= 2;
   }
   g.C = ch;
   g.mv = g.mloc / ch;
